@@ -1,0 +1,548 @@
+// Hand-written sm_100a kernels of the P1 constant-stencil multigrid path.
+//
+// Replaces (on the device) the pystencils-generated host kernels of the reference:
+//   apply_3D_macrocell_vertexdof_to_vertexdof_{replace,add}   (P1generatedKernels/...replace.cpp:33-79)
+//   apply_3D_macroface_one_sided_*, vertexdof::macroedge/macrovertex::apply (P1Operator.hpp:192-320)
+//   sor_3D_macrocell_P1 / sor_3D_macroface_P1                 (sor_3D_macrocell_P1.cpp:32-81)
+//   assign_3D_macrocell_vertexdof_*_rhs_function(s), add_*    (p1functionspace/generatedKernels)
+//   restrict_3D_macrocell_P1_pull_additive, prolongate_3D_macrocell_P1_push_additive
+//   and all "communicate"/"communicateAdditively" ghost-layer copies between primitives.
+// See DESIGN.md for the data layout and the roofline of each kernel.
+#include "kernels.h"
+
+#include "hb_device.h"
+
+#ifdef HB_EMUL
+dim3 threadIdx, blockIdx, blockDim, gridDim;
+#endif
+
+#define HB_WPB 8 // warps (z-slices) per interior block
+#define HB_BLOCK ( HB_WPB * 32 )
+
+// =============================================================================================
+//  Stencil kernel: interior tiles (register marching along y) + boundary points in one launch
+// =============================================================================================
+
+struct HbRow3
+{
+   double l, c, r;
+};
+
+template < bool NC >
+__device__ __forceinline__ double hb_ld( const double* p )
+{
+   // non-coherent (read-only) path only when the kernel never writes the array it reads
+   return NC ? __ldg( p ) : *p;
+}
+
+template < bool NC >
+__device__ __forceinline__ HbRow3 hb_load_row( const double* S, int base, int last, int x )
+{
+   // row occupies S[base .. base+last]; x >= 1
+   HbRow3 v;
+   v.l = ( x - 1 <= last ) ? hb_ld< NC >( S + base + x - 1 ) : 0.0;
+   v.c = ( x <= last ) ? hb_ld< NC >( S + base + x ) : 0.0;
+   v.r = ( x + 1 <= last ) ? hb_ld< NC >( S + base + x + 1 ) : 0.0;
+   return v;
+}
+
+template < int MODE >
+__device__ __forceinline__ void hb_interior_tile( const HbLevelView& lv, const HbStencilArgs& a, int cell, const HbTile t, int warp, int lane )
+{
+   const int N = lv.N;
+   const int z = t.z0 + warp;
+   if ( z > N - 3 )
+      return;
+   const int x     = t.x0 + lane;
+   const int y0    = t.y0;
+   int       yLast = y0 + lv.tileRows - 1;  // last row of this tile
+   if ( yLast > N - 2 - z )
+      yLast = N - 2 - z;
+   if ( yLast > N - 1 - x - z )
+      yLast = N - 1 - x - z;               // this lane is outside the tet beyond that row
+   if ( yLast < y0 )
+      return;
+
+   const HbRegion reg = lv.cells[cell].region[0];
+   if ( !( a.bc.type[reg.bflag] & a.flag ) )
+      return;
+
+   const double* S = a.src[cell];
+   constexpr bool NC = ( MODE != HB_SOR );
+   const double* __restrict__ Wc = a.W + (size_t) cell * HB_NMASK * HB_NDIR;
+   double w[HB_NDIR];
+#pragma unroll
+   for ( int d = 0; d < HB_NDIR; d++ )
+      w[d] = __ldg( Wc + d );
+
+   const int wm     = N + 1 - z;                       // width of slice z
+   const int total  = hb_tet( N + 1 );
+   const int sliceM = total - hb_tet( wm );
+   const int sliceB = total - hb_tet( wm + 1 );
+   const int sliceT = total - hb_tet( wm - 1 );
+   // row base inside a slice of width ws: y*(ws+1) - y(y+1)/2 ; last valid x: ws-1-y
+#define HB_ROWBASE( slice, ws, yy ) ( ( slice ) + ( yy ) * ( ( ws ) + 1 ) - ( ( yy ) * ( ( yy ) + 1 ) ) / 2 )
+
+   HbRow3 P  = hb_load_row< NC >( S, HB_ROWBASE( sliceM, wm, y0 - 1 ), wm - 1 - ( y0 - 1 ), x );
+   HbRow3 C  = hb_load_row< NC >( S, HB_ROWBASE( sliceM, wm, y0 ), wm - 1 - y0, x );
+   HbRow3 B0 = hb_load_row< NC >( S, HB_ROWBASE( sliceB, wm + 1, y0 ), wm - y0, x );
+   HbRow3 T0 = hb_load_row< NC >( S, HB_ROWBASE( sliceT, wm - 1, y0 - 1 ), wm - 2 - ( y0 - 1 ), x );
+
+   const size_t cellOff = (size_t) cell * lv.cellSize;
+   for ( int y = y0; y <= yLast; y++ )
+   {
+      const HbRow3 Nn = hb_load_row< NC >( S, HB_ROWBASE( sliceM, wm, y + 1 ), wm - 1 - ( y + 1 ), x );
+      const HbRow3 B1 = hb_load_row< NC >( S, HB_ROWBASE( sliceB, wm + 1, y + 1 ), wm - ( y + 1 ), x );
+      const HbRow3 T1 = hb_load_row< NC >( S, HB_ROWBASE( sliceT, wm - 1, y ), wm - 2 - y, x );
+
+      double s = w[D_W] * C.l;
+      s += w[D_E] * C.r;
+      s += w[D_N] * Nn.c;
+      s += w[D_NW] * Nn.l;
+      s += w[D_S] * P.c;
+      s += w[D_SE] * P.r;
+      s += w[D_BC] * B0.c;
+      s += w[D_BE] * B0.r;
+      s += w[D_BN] * B1.c;
+      s += w[D_BNW] * B1.l;
+      s += w[D_TC] * T1.c;
+      s += w[D_TW] * T1.l;
+      s += w[D_TS] * T0.c;
+      s += w[D_TSE] * T0.r;
+
+      const size_t gi = cellOff + (size_t) ( HB_ROWBASE( sliceM, wm, y ) + x );
+      if ( MODE != HB_SOR || ( ( x + 2 * y + 3 * z ) & 3 ) == a.colour )
+         hb_epilogue< MODE >( a, a.dst + gi, gi, s, w[D_C], C.c );
+
+      P  = C;
+      C  = Nn;
+      B0 = B1;
+      T0 = T1;
+   }
+#undef HB_ROWBASE
+}
+
+template < int MODE >
+__device__ __forceinline__ void hb_boundary_item( const HbLevelView& lv, const HbStencilArgs& a, long long item )
+{
+   const int cell = (int) ( item / lv.nBnd );
+   const int i    = (int) ( item - (long long) cell * lv.nBnd );
+   if ( cell >= lv.nCells )
+      return;
+   const HbBndPoint p   = lv.bnd[i];
+   const HbRegion   reg = lv.cells[cell].region[p.mask];
+   if ( !( a.bc.type[reg.bflag] & a.flag ) )
+      return;
+   if ( !( ( a.dimSel >> reg.dim ) & 1 ) )
+      return;
+   double sNb, diag;
+   hb_boundary_stencil( lv, a.W, a.src, cell, p.x, p.y, p.z, sNb, diag );
+   const size_t gi     = (size_t) cell * lv.cellSize + hb_index( lv.N, p.x, p.y, p.z );
+   const double centre = a.src[cell][gi - (size_t) cell * lv.cellSize];
+   double*      out    = a.toScratch ? ( a.scratch + item ) : ( a.dst + gi );
+   hb_epilogue< MODE >( a, out, gi, sNb, diag, centre );
+}
+
+// grid = nInteriorBlocks + nBoundaryBlocks.  Interior block b -> (cell, tile); its 8 warps take 8
+// consecutive z-slices of the same (y,x) tile so that the slices shared between neighbouring warps
+// are served by L1 instead of L2.
+template < int MODE >
+__global__ void __launch_bounds__( HB_BLOCK )
+    hb_stencil_kernel( const HbLevelView lv, const HbStencilArgs a, const int nInteriorBlocks, const int doBoundary )
+{
+   const int b = blockIdx.x;
+   if ( b < nInteriorBlocks )
+   {
+      const int    cell = b / lv.nTiles;
+      const HbTile t    = lv.tiles[b - cell * lv.nTiles];
+      hb_interior_tile< MODE >( lv, a, cell, t, threadIdx.x >> 5, threadIdx.x & 31 );
+   }
+   else if ( doBoundary )
+   {
+      const long long item = (long long) ( b - nInteriorBlocks ) * blockDim.x + threadIdx.x;
+      hb_boundary_item< MODE >( lv, a, item );
+   }
+}
+
+// scratch -> dst for the interface phases of SOR
+__global__ void hb_commit_kernel( const HbLevelView lv, const HbStencilArgs a )
+{
+   const long long item = (long long) blockIdx.x * blockDim.x + threadIdx.x;
+   const int       cell = (int) ( item / lv.nBnd );
+   if ( cell >= lv.nCells )
+      return;
+   const int        i   = (int) ( item - (long long) cell * lv.nBnd );
+   const HbBndPoint p   = lv.bnd[i];
+   const HbRegion   reg = lv.cells[cell].region[p.mask];
+   if ( !( a.bc.type[reg.bflag] & a.flag ) )
+      return;
+   if ( !( ( a.dimSel >> reg.dim ) & 1 ) )
+      return;
+   a.dst[(size_t) cell * lv.cellSize + hb_index( lv.N, p.x, p.y, p.z )] = a.scratch[item];
+}
+
+template < int MODE >
+static void hb_launch_stencil_mode( const HbLevelView& lv, const HbStencilArgs& a, bool interior, bool boundary, cudaStream_t st )
+{
+   const long long nIntBlocks = interior ? (long long) lv.nCells * lv.nTiles : 0;
+   const long long nBndItems  = boundary ? (long long) lv.nCells * lv.nBnd : 0;
+   const long long nBndBlocks = ( nBndItems + HB_BLOCK - 1 ) / HB_BLOCK;
+   const long long grid       = nIntBlocks + nBndBlocks;
+   if ( grid == 0 )
+      return;
+   HB_LAUNCH( hb_stencil_kernel< MODE >, (unsigned) grid, HB_BLOCK, st, lv, a, (int) nIntBlocks, boundary ? 1 : 0 );
+}
+
+void hb_launch_stencil( int mode, const HbLevelView& lv, const HbStencilArgs& a, bool interior, bool boundary, cudaStream_t st )
+{
+   switch ( mode )
+   {
+   case HB_APPLY_REPLACE:
+      hb_launch_stencil_mode< HB_APPLY_REPLACE >( lv, a, interior, boundary, st );
+      break;
+   case HB_APPLY_ADD:
+      hb_launch_stencil_mode< HB_APPLY_ADD >( lv, a, interior, boundary, st );
+      break;
+   case HB_RESIDUAL:
+      hb_launch_stencil_mode< HB_RESIDUAL >( lv, a, interior, boundary, st );
+      break;
+   case HB_JACOBI:
+      hb_launch_stencil_mode< HB_JACOBI >( lv, a, interior, boundary, st );
+      break;
+   case HB_SOR:
+      hb_launch_stencil_mode< HB_SOR >( lv, a, interior, boundary, st );
+      break;
+   case HB_CHEB_FIRST:
+      hb_launch_stencil_mode< HB_CHEB_FIRST >( lv, a, interior, boundary, st );
+      break;
+   case HB_CHEB_STEP:
+      hb_launch_stencil_mode< HB_CHEB_STEP >( lv, a, interior, boundary, st );
+      break;
+   case HB_DIAG:
+      hb_launch_stencil_mode< HB_DIAG >( lv, a, interior, boundary, st );
+      break;
+   case HB_INVDIAG:
+      hb_launch_stencil_mode< HB_INVDIAG >( lv, a, interior, boundary, st );
+      break;
+   }
+}
+
+void hb_launch_commit( const HbLevelView& lv, const HbStencilArgs& a, cudaStream_t st )
+{
+   const long long n = (long long) lv.nCells * lv.nBnd;
+   if ( n == 0 )
+      return;
+   HB_LAUNCH( hb_commit_kernel, (unsigned) ( ( n + 255 ) / 256 ), 256, st, lv, a );
+}
+
+// =============================================================================================
+//  BLAS-1 (flat over the local arena; boundary mask template decides DoFType / ownership)
+// =============================================================================================
+
+__device__ __forceinline__ bool hb_point_selected( const HbLevelView& lv, const HbBC& bc, int flag, size_t gi, bool ownerOnly )
+{
+   const int cell  = (int) ( gi / (size_t) lv.cellSize );
+   const int local = (int) ( gi - (size_t) cell * lv.cellSize );
+   const int m     = lv.mask[local];
+   const HbRegion r = lv.cells[cell].region[m];
+   if ( ownerOnly && !r.owner )
+      return false;
+   return ( bc.type[r.bflag] & flag ) != 0;
+}
+
+// dst = sum_k c[k]*src[k]  (+ dst if accumulate)
+__global__ void hb_lincomb_kernel( const HbLevelView lv, const HbLinComb lc )
+{
+   const size_t n      = (size_t) lv.nCells * lv.cellSize;
+   const size_t stride = (size_t) gridDim.x * blockDim.x;
+   for ( size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride )
+   {
+      if ( lc.flag != HB_DOF_ALL && !hb_point_selected( lv, lc.bc, lc.flag, i, false ) )
+         continue;
+      double v = lc.accumulate ? lc.dst[i] : 0.0;
+      if ( lc.n > 0 )
+         v += lc.c[0] * lc.src[0][i];
+      if ( lc.n > 1 )
+         v += lc.c[1] * lc.src[1][i];
+      if ( lc.n > 2 )
+         v += lc.c[2] * lc.src[2][i];
+      if ( lc.n > 3 )
+         v += lc.c[3] * lc.src[3][i];
+      v += lc.shift;
+      lc.dst[i] = v;
+   }
+}
+
+// dst = prod_k src[k]
+__global__ void hb_multelem_kernel( const HbLevelView lv, const HbLinComb lc )
+{
+   const size_t n      = (size_t) lv.nCells * lv.cellSize;
+   const size_t stride = (size_t) gridDim.x * blockDim.x;
+   for ( size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride )
+   {
+      if ( lc.flag != HB_DOF_ALL && !hb_point_selected( lv, lc.bc, lc.flag, i, false ) )
+         continue;
+      double v = lc.src[0][i];
+      for ( int k = 1; k < lc.n; k++ )
+         v *= lc.src[k][i];
+      lc.dst[i] = v;
+   }
+}
+
+// partial[b] = reduction over owned points: op 0: sum a*b, 1: sum a, 2: max |a|
+__global__ void hb_reduce_kernel( const HbLevelView lv, const HbBC bc, int flag, int op, const double* a, const double* b, double* partial )
+{
+   const size_t n      = (size_t) lv.nCells * lv.cellSize;
+   const size_t stride = (size_t) gridDim.x * blockDim.x;
+   double       acc    = 0.0;
+   for ( size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride )
+   {
+      if ( !hb_point_selected( lv, bc, flag, i, true ) )
+         continue;
+      if ( op == 0 )
+         acc += a[i] * b[i];
+      else if ( op == 1 )
+         acc += a[i];
+      else
+         acc = fmax( acc, fabs( a[i] ) );
+   }
+#ifdef HB_EMUL
+   if ( threadIdx.x == 0 )
+      partial[blockIdx.x] = acc;
+   else if ( op == 2 )
+      partial[blockIdx.x] = fmax( partial[blockIdx.x], acc );
+   else
+      partial[blockIdx.x] += acc;
+#else
+   __shared__ double sm[32];
+   for ( int o = 16; o > 0; o >>= 1 )
+   {
+      const double other = __shfl_down_sync( 0xffffffffu, acc, o );
+      acc                = ( op == 2 ) ? fmax( acc, other ) : acc + other;
+   }
+   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+   if ( lane == 0 )
+      sm[warp] = acc;
+   __syncthreads();
+   if ( warp == 0 )
+   {
+      const int nw = blockDim.x >> 5;
+      acc          = lane < nw ? sm[lane] : 0.0;
+      for ( int o = 16; o > 0; o >>= 1 )
+      {
+         const double other = __shfl_down_sync( 0xffffffffu, acc, o );
+         acc                = ( op == 2 ) ? fmax( acc, other ) : acc + other;
+      }
+      if ( lane == 0 )
+         partial[blockIdx.x] = acc;
+   }
+#endif
+}
+
+// out[slot] = reduction of partial[0..n) in fixed order (single block)
+__global__ void hb_reduce_final_kernel( const double* partial, int n, int op, double* out )
+{
+#ifdef HB_EMUL
+   double acc = 0.0;
+   for ( int i = 0; i < n; i++ )
+      acc = ( op == 2 ) ? fmax( acc, partial[i] ) : acc + partial[i];
+   *out = acc;
+#else
+   __shared__ double sm[32];
+   double            acc = 0.0;
+   for ( int i = threadIdx.x; i < n; i += blockDim.x )
+      acc = ( op == 2 ) ? fmax( acc, partial[i] ) : acc + partial[i];
+   for ( int o = 16; o > 0; o >>= 1 )
+   {
+      const double other = __shfl_down_sync( 0xffffffffu, acc, o );
+      acc                = ( op == 2 ) ? fmax( acc, other ) : acc + other;
+   }
+   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+   if ( lane == 0 )
+      sm[warp] = acc;
+   __syncthreads();
+   if ( warp == 0 )
+   {
+      const int nw = blockDim.x >> 5;
+      acc          = lane < nw ? sm[lane] : 0.0;
+      for ( int o = 16; o > 0; o >>= 1 )
+      {
+         const double other = __shfl_down_sync( 0xffffffffu, acc, o );
+         acc                = ( op == 2 ) ? fmax( acc, other ) : acc + other;
+      }
+      if ( lane == 0 )
+         *out = acc;
+   }
+#endif
+}
+
+static int hb_flat_grid( size_t n, int block, int maxBlocks )
+{
+   size_t g = ( n + block - 1 ) / block;
+   if ( g > (size_t) maxBlocks )
+      g = maxBlocks;
+   if ( g < 1 )
+      g = 1;
+   return (int) g;
+}
+
+void hb_launch_lincomb( const HbLevelView& lv, const HbLinComb& lc, cudaStream_t st )
+{
+   const size_t n = (size_t) lv.nCells * lv.cellSize;
+   if ( n == 0 )
+      return;
+   HB_LAUNCH( hb_lincomb_kernel, hb_flat_grid( n, 256, 148 * 16 ), 256, st, lv, lc );
+}
+
+void hb_launch_multelem( const HbLevelView& lv, const HbLinComb& lc, cudaStream_t st )
+{
+   const size_t n = (size_t) lv.nCells * lv.cellSize;
+   if ( n == 0 )
+      return;
+   HB_LAUNCH( hb_multelem_kernel, hb_flat_grid( n, 256, 148 * 16 ), 256, st, lv, lc );
+}
+
+void hb_launch_reduce( const HbLevelView& lv, const HbBC& bc, int flag, int op, const double* a, const double* b, double* partial, double* out, cudaStream_t st )
+{
+   const size_t n = (size_t) lv.nCells * lv.cellSize;
+#ifdef HB_EMUL
+   const int block = 1;
+#else
+   const int block = 256;
+#endif
+   const int grid = hb_flat_grid( n, 256, HB_REDUCE_MAX_BLOCKS );
+   HB_LAUNCH( hb_reduce_kernel, grid, block, st, lv, bc, flag, op, a, b, partial );
+   HB_LAUNCH( hb_reduce_final_kernel, 1, block, st, partial, grid, op, out );
+}
+
+// =============================================================================================
+//  Grid transfer (gather form)
+// =============================================================================================
+
+// Full-weighting restriction fine -> coarse = transpose of linear interpolation.
+// reference P1toP1LinearRestriction::restrict3D (P1toP1LinearRestriction.cpp:169-346) and
+// restrict_3D_macrocell_P1_pull_additive: leaves on a macro face/edge/vertex are shared between
+// macro-cells and therefore divided by the number of cells sharing that primitive; the additive
+// communication of the reference becomes the sum over the copies of the coarse point.
+__device__ __forceinline__ double hb_restrict_partial( const HbLevelView& fine, const double* f, int slot, int xc, int yc, int zc )
+{
+   // coarse point (xc,yc,zc) in macro-cell 'slot'; fine level N = 2*coarse N
+   const int        Nf = fine.N;
+   const int        x = 2 * xc, y = 2 * yc, z = 2 * zc;
+   const int        m = hb_mask( Nf, x, y, z );
+   const int        vm = hb_valid[m];
+   const HbRegion*  reg = fine.cells[slot].region;
+   double           acc = f[hb_index( Nf, x, y, z )] / (double) reg[m].mult;
+#pragma unroll
+   for ( int d = 1; d < HB_NDIR; d++ )
+      if ( ( vm >> d ) & 1 )
+      {
+         const int xx = x + hb_dir[d][0], yy = y + hb_dir[d][1], zz = z + hb_dir[d][2];
+         const int mm = hb_mask( Nf, xx, yy, zz );
+         acc += 0.5 * f[hb_index( Nf, xx, yy, zz )] / (double) reg[mm].mult;
+      }
+   return acc;
+}
+
+__global__ void hb_restrict_kernel( const HbLevelView coarse, const HbLevelView fine, const double* const* fsrc, double* cdst, const HbBC bc, int flag )
+{
+   const size_t n      = (size_t) coarse.nCells * coarse.cellSize;
+   const size_t stride = (size_t) gridDim.x * blockDim.x;
+   const int    N      = coarse.N;
+   for ( size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride )
+   {
+      const int cell  = (int) ( i / (size_t) coarse.cellSize );
+      const int local = (int) ( i - (size_t) cell * coarse.cellSize );
+      {
+         const HbBndPoint q = coarse.xyz[local];
+         const int        x = q.x, y = q.y, z = q.z;
+         const int m = hb_mask( N, x, y, z );
+         const HbCellInfo ci = coarse.cells[cell];
+         if ( !( bc.type[ci.region[m].bflag] & flag ) )
+            continue;
+         double acc = 0.0;
+         if ( m == 0 )
+            acc = hb_restrict_partial( fine, fsrc[cell], cell, x, y, z );
+         else
+         {
+            const int b[4] = { N - x - y - z, x, y, z };
+            int       supp = 0;
+            for ( int j = 0; j < 4; j++ )
+               supp |= ( b[j] != 0 ) << j;
+            for ( int e = ci.copyBegin; e < ci.copyEnd; e++ )
+            {
+               const HbCopy cp = coarse.copies[e];
+               if ( supp & ~cp.sharedMask )
+                  continue;
+               int bp[4] = { 0, 0, 0, 0 };
+               for ( int j = 0; j < 4; j++ )
+                  if ( ( supp >> j ) & 1 )
+                     bp[cp.vmap[j]] = b[j];
+               acc += hb_restrict_partial( fine, fsrc[cp.slot], cp.slot, bp[1], bp[2], bp[3] );
+            }
+         }
+         cdst[i] = acc;
+      }
+   }
+}
+
+// Linear prolongation coarse -> fine, gather form: every fine point is either a coarse point or the
+// midpoint of exactly one coarse micro-edge, whose direction is given by the parity of (x,y,z).
+// reference P1toP1LinearProlongation::prolongate3DAdditively (P1toP1LinearProlongation.cpp:194-410).
+__global__ void hb_prolongate_kernel( const HbLevelView coarse, const HbLevelView fine, const double* csrc, double* fdst, const HbBC bc, int flag, int add )
+{
+   const size_t n      = (size_t) fine.nCells * fine.cellSize;
+   const size_t stride = (size_t) gridDim.x * blockDim.x;
+   const int    Nf = fine.N, Nc = coarse.N;
+   for ( size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride )
+   {
+      const int cell  = (int) ( i / (size_t) fine.cellSize );
+      const int local = (int) ( i - (size_t) cell * fine.cellSize );
+      const HbBndPoint q = fine.xyz[local];
+      const int        x = q.x, y = q.y, z = q.z;
+      const int m = hb_mask( Nf, x, y, z );
+      if ( !( bc.type[fine.cells[cell].region[m].bflag] & flag ) )
+         continue;
+      const double* c  = csrc + (size_t) cell * coarse.cellSize;
+      const int     px = x & 1, py = y & 1, pz = z & 1;
+      double        v;
+      if ( !( px | py | pz ) )
+         v = c[hb_index( Nc, x >> 1, y >> 1, z >> 1 )];
+      else
+      {
+         // edge direction with that parity: (1,0,0) (0,1,0) (0,0,1) (1,-1,0) (1,0,-1) (0,1,-1) (1,-1,1)
+         int dx = px, dy = py, dz = pz;
+         if ( px && py )
+            dy = -1;
+         else if ( px && pz )
+            dz = -1;
+         else if ( py && pz )
+            dz = -1;
+         if ( px && py && pz )
+         {
+            dy = -1;
+            dz = 1;
+         }
+         const int ax = ( x - dx ) >> 1, ay = ( y - dy ) >> 1, az = ( z - dz ) >> 1;
+         const int bx = ( x + dx ) >> 1, by = ( y + dy ) >> 1, bz = ( z + dz ) >> 1;
+         v            = 0.5 * c[hb_index( Nc, ax, ay, az )] + 0.5 * c[hb_index( Nc, bx, by, bz )];
+      }
+      fdst[i] = add ? fdst[i] + v : v;
+   }
+}
+
+void hb_launch_restrict( const HbLevelView& coarse, const HbLevelView& fine, const double* const* fsrc, double* cdst, const HbBC& bc, int flag, cudaStream_t st )
+{
+   const size_t n = (size_t) coarse.nCells * coarse.cellSize;
+   if ( n == 0 )
+      return;
+   HB_LAUNCH( hb_restrict_kernel, hb_flat_grid( n, 256, 148 * 16 ), 256, st, coarse, fine, fsrc, cdst, bc, flag );
+}
+
+void hb_launch_prolongate( const HbLevelView& coarse, const HbLevelView& fine, const double* csrc, double* fdst, const HbBC& bc, int flag, int add, cudaStream_t st )
+{
+   const size_t n = (size_t) fine.nCells * fine.cellSize;
+   if ( n == 0 )
+      return;
+   HB_LAUNCH( hb_prolongate_kernel, hb_flat_grid( n, 256, 148 * 16 ), 256, st, coarse, fine, csrc, fdst, bc, flag, add );
+}

@@ -1,0 +1,160 @@
+/* hyteg_b200 -- C-ABI of the B200-native matrix-free P1 geometric-multigrid path.
+ *
+ * This is the drop-in boundary: plain pointers, sizes and opaque handles, no C++/torch types.  Each
+ * entry point names the HyTeG interface it stands in for (paths relative to the reference tree).
+ * The C++ header include/hyteg_b200/hyteg.hpp wraps these calls in classes with HyTeG's own names
+ * (P1Function, P1ConstantLaplaceOperator, GeometricMultigridSolver, ...); INTEGRATION.md shows the
+ * reference-side binding.
+ *
+ * Conventions: every function returning int returns 0 on success and a non-zero code on failure,
+ * with the message available from hb_last_error().  All device work is enqueued on the stream set
+ * by hb_set_stream() (default: the legacy default stream); calls that return values to the host
+ * synchronise that stream.  DoFType / UpdateType values are HyTeG's (src/hyteg/types/types.hpp:29-44).
+ */
+#ifndef HYTEG_B200_H
+#define HYTEG_B200_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct hb_storage  hb_storage;  /* PrimitiveStorage (macro mesh + per-level device tables) */
+typedef struct hb_function hb_function; /* P1Function<double>                                       */
+typedef struct hb_operator hb_operator; /* P1ConstantLaplaceOperator                                */
+typedef struct hb_solver   hb_solver;   /* Solver<P1ConstantLaplaceOperator>                        */
+
+enum
+{
+   HB_None              = 0,
+   HB_Inner             = 1,
+   HB_DirichletBoundary = 2,
+   HB_NeumannBoundary   = 4,
+   HB_FreeslipBoundary  = 8,
+   HB_Boundary          = 14,
+   HB_All               = 15
+};
+enum
+{
+   HB_Replace = 0,
+   HB_Add     = 1
+};
+enum
+{
+   HB_VCYCLE = 0,
+   HB_WCYCLE = 1
+};
+
+/* ---- runtime ---------------------------------------------------------------------------------- */
+const char* hb_last_error( void );
+const char* hb_version( void );
+int         hb_device_init( int device );         /* cudaSetDevice; fails loudly without a CUDA device */
+int         hb_set_stream( void* cuda_stream );    /* cudaStream_t to enqueue all subsequent work on     */
+int         hb_synchronize( void );
+/* Sum/max reduction across ranks, installed by the host plumbing (NCCL/torch.distributed); stands in
+ * for walberla::mpi::allReduceInplace (src/hyteg/p1functionspace/VertexDoFFunction.cpp:1714).
+ * op: 0 sum, 2 max.  buf is a HOST buffer of n doubles. */
+typedef void ( *hb_allreduce_fn )( double* buf, int n, int op, void* ctx );
+int hb_set_allreduce( hb_allreduce_fn fn, void* ctx );
+/* tuning knobs for kernel experiments: "tile_rows" */
+int hb_set_tuning( const char* key, int value );
+
+/* ---- PrimitiveStorage  (src/hyteg/primitivestorage/SetupPrimitiveStorage.hpp, PrimitiveStorage.hpp) */
+/* cells: 4 vertex ids per macro-tet, in mesh order (MeshInfo).  Macro-cells are distributed over
+ * n_ranks in contiguous blocks; this process keeps the cells of 'rank'. */
+hb_storage* hb_storage_create( int n_vertices, const double* xyz, int n_cells, const int* cells, int rank, int n_ranks );
+void        hb_storage_destroy( hb_storage* st );
+/* SetupPrimitiveStorage::setMeshBoundaryFlagsOnBoundary (SetupPrimitiveStorage.cpp:977-988) */
+int hb_storage_set_mesh_boundary_flags_on_boundary( hb_storage* st, int flag_on_boundary, int flag_inner, int highest_dim_always_inner );
+/* counts[4] = number of macro vertices, edges, faces, cells (global) */
+int hb_storage_counts( const hb_storage* st, int* counts );
+/* dim 0..3: vertex ids of every primitive of that dimension (1,2,3,4 ints each) */
+int hb_storage_primitive_vertices( const hb_storage* st, int dim, int* out );
+int hb_storage_get_mesh_boundary_flags( const hb_storage* st, int dim, int* out );
+int hb_storage_set_mesh_boundary_flags( hb_storage* st, int dim, const int* in ); /* Primitive::meshBoundaryFlag_ */
+int hb_storage_num_local_cells( const hb_storage* st );
+int hb_storage_local_cell_global_id( const hb_storage* st, int local_cell );
+/* levelinfo::num_microvertices_per_cell (src/hyteg/Levelinfo.hpp:101-105) */
+long long hb_cell_array_size( int level );
+/* numberOfGlobalDoFs<P1FunctionTag> (src/hyteg/functions/FunctionProperties.hpp) */
+long long hb_storage_num_global_dofs( const hb_storage* st, int level );
+/* coordinates of every entry of the local arena on 'level': xyz[3 * n_local_cells * cell_array_size] */
+int hb_storage_micro_coordinates( const hb_storage* st, int level, double* xyz );
+
+/* ---- P1Function  (src/hyteg/p1functionspace/VertexDoFFunction.hpp/.cpp) ------------------------- */
+hb_function* hb_p1function_create( hb_storage* st, int min_level, int max_level );
+void         hb_p1function_destroy( hb_function* f );
+/* BoundaryCondition: meshBoundaryFlag -> DoFType; default create0123BC (0 Inner,1 Dirichlet,2 Neumann,3 Freeslip) */
+int hb_p1function_set_boundary_condition( hb_function* f, const int* dof_type_of_flag, int n );
+/* Whole local arena (n_local_cells * cell_array_size doubles, macro-cell after macro-cell, each in
+ * HyTeG's macro-cell layout, src/hyteg/indexing/MacroCellIndexing.hpp:44-52).  Only DoFs whose
+ * primitive matches 'flag' are written (interpolate semantics, VertexDoFFunction.cpp interpolate). */
+int hb_p1function_upload( hb_function* f, int level, const double* host, int flag );
+int hb_p1function_download( const hb_function* f, int level, double* host );
+int hb_p1function_upload_cell( hb_function* f, int level, int local_cell, const double* host );
+int hb_p1function_download_cell( const hb_function* f, int level, int local_cell, double* host );
+/* raw device pointer of the local arena (for zero-copy interop, e.g. torch tensors) */
+double* hb_p1function_device_ptr( hb_function* f, int level );
+/* interpolate( constant, level, flag ) */
+int hb_p1function_interpolate_constant( hb_function* f, double value, int level, int flag );
+/* assign / add: dst (+)= sum_k scalars[k] * srcs[k]   (VertexDoFFunction::assign/add, n <= 4) */
+int hb_p1function_assign( hb_function* dst, int n, const double* scalars, hb_function* const* srcs, int level, int flag );
+int hb_p1function_add( hb_function* dst, int n, const double* scalars, hb_function* const* srcs, int level, int flag );
+int hb_p1function_add_scalar( hb_function* dst, double scalar, int level, int flag );
+/* multElementwise: dst = prod_k srcs[k] */
+int hb_p1function_mult_elementwise( hb_function* dst, int n, hb_function* const* srcs, int level, int flag );
+/* dotGlobal / sumGlobal / getMaxDoFMagnitude (every DoF counted once; all-reduced when a reducer is set) */
+int hb_p1function_dot( const hb_function* a, const hb_function* b, int level, int flag, double* out );
+int hb_p1function_sum( const hb_function* a, int level, int flag, double* out );
+int hb_p1function_max_magnitude( const hb_function* a, int level, int flag, double* out );
+
+/* ---- P1ConstantLaplaceOperator  (src/constant_stencil_operator/P1ConstantOperator.hpp,
+ *      src/hyteg/p1functionspace/P1Operator.hpp:192-447, src/hyteg/operators/Operator.hpp:76-83) ---- */
+hb_operator* hb_p1_constant_laplace_create( hb_storage* st, int min_level, int max_level );
+void         hb_operator_destroy( hb_operator* op );
+/* Operator::apply( src, dst, level, flag, updateType ) */
+int hb_operator_apply( hb_operator* op, const hb_function* src, hb_function* dst, int level, int flag, int update_type );
+/* P1Operator::smooth_jac( dst, rhs, src, omega, level, flag )  (P1Operator.hpp:429-447), one fused kernel */
+int hb_operator_smooth_jac( hb_operator* op, hb_function* dst, const hb_function* rhs, const hb_function* src, double omega, int level, int flag );
+/* P1Operator::smooth_sor / smooth_sor_backwards / smooth_gs (P1Operator.hpp:322-427): multicolour ordering */
+int hb_operator_smooth_sor( hb_operator* op, hb_function* dst, const hb_function* rhs, double omega, int level, int flag, int backwards );
+/* fused r = b - A x  (GeometricMultigridSolver.hpp:255-259 does apply + assign) */
+int hb_operator_residual( hb_operator* op, const hb_function* x, const hb_function* b, hb_function* r, int level, int flag );
+/* fused Chebyshev building blocks (ChebyshevSmoother.hpp:179-222):
+ *   first: dst = D^-1 (b - A x);   step: dst = D^-1 A src, x += coeff * src */
+int hb_operator_cheb_first( hb_operator* op, const hb_function* x, const hb_function* b, hb_function* dst, int level, int flag );
+int hb_operator_cheb_step( hb_operator* op, const hb_function* src, hb_function* dst, hb_function* x, double coeff, int level, int flag );
+/* computeDiagonalOperatorValues / computeInverseDiagonalOperatorValues (P1Operator.hpp:452-465) into f */
+int hb_operator_diagonal( hb_operator* op, hb_function* f, int level, int inverse );
+/* the 15 macro-cell stencil weights of a local macro-cell for boundary mask 'mask' (0 = interior), order:
+ * C W E N S NW SE TC TW TS TSE BC BN BE BNW  (P1ConstantOperator cell stencil, P1Elements.hpp) */
+int hb_operator_cell_stencil( const hb_operator* op, int level, int local_cell, int mask, double* w15 );
+
+/* ---- P1toP1LinearRestriction / P1toP1LinearProlongation (src/hyteg/gridtransferoperators/) ------- */
+int hb_p1_restrict( hb_function* f, int source_level, int flag );            /* restrict( f, sourceLevel, flag ) */
+int hb_p1_prolongate( hb_function* f, int source_level, int flag );          /* prolongate( f, sourceLevel, flag ) */
+int hb_p1_prolongate_and_add( hb_function* f, int source_level, int flag );  /* prolongateAndAdd */
+
+/* ---- Solvers (src/hyteg/solvers/) ------------------------------------------------------------------ */
+hb_solver* hb_solver_create_cg( hb_storage* st, int min_level, int max_level, int max_iter, double rel_tol, double abs_tol ); /* CGSolver.hpp:44-91 */
+hb_solver* hb_solver_create_weighted_jacobi( hb_storage* st, int min_level, int max_level, double omega ); /* WeightedJacobiSmoother.hpp */
+hb_solver* hb_solver_create_sor( double omega );                                                            /* SORSmoother.hpp */
+hb_solver* hb_solver_create_gauss_seidel( void );                                                           /* GaussSeidelSmoother.hpp */
+hb_solver* hb_solver_create_symmetric_gauss_seidel( void );                                                 /* SymmetricGaussSeidelSmoother.hpp */
+hb_solver* hb_solver_create_chebyshev( hb_storage* st, int min_level, int max_level );                      /* ChebyshevSmoother.hpp */
+/* ChebyshevSmoother::setupCoefficients( order, spectralRadius ) / ( order, lower, upper ) (:240-276) */
+int hb_chebyshev_setup_coefficients( hb_solver* cheb, int order, double lower_bound, double upper_bound );
+int hb_chebyshev_coefficients( const hb_solver* cheb, double* coeffs, int* n );
+/* chebyshev::estimateRadius (ChebyshevSmoother.hpp:637-647 -> numerictools/SpectrumEstimation.hpp:56-85):
+ * power iteration on D^-1 A starting from x (overwritten) */
+int hb_estimate_spectral_radius( hb_operator* op, hb_function* x, hb_function* tmp, int iterations, int level, double* radius );
+/* GeometricMultigridSolver (GeometricMultigridSolver.hpp:61-96) with P1 linear transfer operators */
+hb_solver* hb_solver_create_gmg( hb_storage* st, hb_solver* smoother, hb_solver* coarse_solver, int min_level, int max_level,
+                                 int pre_smooth, int post_smooth, int smooth_increment, int cycle_type );
+int        hb_solver_solve( hb_solver* s, hb_operator* op, hb_function* x, hb_function* b, int level ); /* Solver::solve */
+int        hb_solver_iterations( const hb_solver* s );
+void       hb_solver_destroy( hb_solver* s );
+
+#ifdef __cplusplus
+}
+#endif
+#endif
