@@ -1,0 +1,283 @@
+"""Python mirror of the HyTeG interfaces of the P1 multigrid path, over the C-ABI.
+
+Class and method names follow the reference (P1Function, P1ConstantLaplaceOperator,
+GeometricMultigridSolver, ...; see include/hyteg_b200/hyteg.hpp for the file:line citations) so the
+parity tests read like HyTeG's own tests.  All arithmetic runs in the CUDA library.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import capi
+from .capi import (Add, All, Boundary, DirichletBoundary, FreeslipBoundary, Inner, NeumannBoundary,
+                   Replace, VCYCLE, WCYCLE, as_dp, as_ip, f64, i32)
+
+SMOOTH_FLAG = Inner | NeumannBoundary | FreeslipBoundary
+
+
+class PrimitiveStorage:
+    """SetupPrimitiveStorage + PrimitiveStorage for tetrahedral macro meshes."""
+
+    def __init__(self, vertices, cells, rank=0, n_ranks=1, lib=None):
+        self.lib = lib or capi.get_lib()
+        self.vertices = f64(vertices).reshape(-1, 3)
+        self.cells = i32(cells).reshape(-1, 4)
+        self.h = self.lib.checkp(self.lib.dll.hb_storage_create(
+            len(self.vertices), as_dp(self.vertices), len(self.cells), as_ip(self.cells), rank, n_ranks))
+        self.rank, self.n_ranks = rank, n_ranks
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.lib.dll.hb_storage_destroy(self.h)
+            self.h = None
+
+    def setMeshBoundaryFlagsOnBoundary(self, flag_on_boundary, flag_inner, highest_dim_always_inner):
+        self.lib.check(self.lib.dll.hb_storage_set_mesh_boundary_flags_on_boundary(
+            self.h, flag_on_boundary, flag_inner, int(highest_dim_always_inner)))
+
+    def counts(self):
+        c = np.zeros(4, dtype=np.int32)
+        self.lib.check(self.lib.dll.hb_storage_counts(self.h, as_ip(c)))
+        return tuple(int(x) for x in c)
+
+    def primitive_vertices(self, dim):
+        n = self.counts()[dim]
+        out = np.zeros((n, dim + 1), dtype=np.int32)
+        self.lib.check(self.lib.dll.hb_storage_primitive_vertices(self.h, dim, as_ip(out)))
+        return out
+
+    def get_mesh_boundary_flags(self, dim):
+        out = np.zeros(self.counts()[dim], dtype=np.int32)
+        self.lib.check(self.lib.dll.hb_storage_get_mesh_boundary_flags(self.h, dim, as_ip(out)))
+        return out
+
+    def set_mesh_boundary_flags(self, dim, flags):
+        flags = i32(flags)
+        assert len(flags) == self.counts()[dim]
+        self.lib.check(self.lib.dll.hb_storage_set_mesh_boundary_flags(self.h, dim, as_ip(flags)))
+
+    @property
+    def num_local_cells(self):
+        return self.lib.dll.hb_storage_num_local_cells(self.h)
+
+    def local_cell_global_ids(self):
+        return [self.lib.dll.hb_storage_local_cell_global_id(self.h, i) for i in range(self.num_local_cells)]
+
+    def cell_array_size(self, level):
+        return int(self.lib.dll.hb_cell_array_size(level))
+
+    def num_global_dofs(self, level):
+        return int(self.lib.dll.hb_storage_num_global_dofs(self.h, level))
+
+    def micro_coordinates(self, level):
+        n = self.num_local_cells * self.cell_array_size(level)
+        xyz = np.zeros((n, 3))
+        self.lib.check(self.lib.dll.hb_storage_micro_coordinates(self.h, level, as_dp(xyz)))
+        return xyz
+
+
+class P1Function:
+    def __init__(self, name, storage, min_level, max_level):
+        self.name, self.storage, self.lib = name, storage, storage.lib
+        self.min_level, self.max_level = min_level, max_level
+        self.h = self.lib.checkp(self.lib.dll.hb_p1function_create(storage.h, min_level, max_level))
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.lib.dll.hb_p1function_destroy(self.h)
+            self.h = None
+
+    def _n(self, level):
+        return self.storage.num_local_cells * self.storage.cell_array_size(level)
+
+    def setBoundaryCondition(self, types):
+        t = i32(types)
+        self.lib.check(self.lib.dll.hb_p1function_set_boundary_condition(self.h, as_ip(t), len(t)))
+
+    def interpolate(self, expr, level, flag=All):
+        if callable(expr):
+            xyz = self.storage.micro_coordinates(level)
+            vals = f64(expr(xyz[:, 0], xyz[:, 1], xyz[:, 2]) * np.ones(len(xyz)))
+            self.upload(vals, level, flag)
+        else:
+            self.lib.check(self.lib.dll.hb_p1function_interpolate_constant(self.h, float(expr), level, flag))
+
+    def setToZero(self, level):
+        self.interpolate(0.0, level, All)
+
+    def upload(self, values, level, flag=All):
+        v = f64(values).ravel()
+        assert v.size == self._n(level), (v.size, self._n(level))
+        self.lib.check(self.lib.dll.hb_p1function_upload(self.h, level, as_dp(v), flag))
+
+    def download(self, level):
+        out = np.zeros(self._n(level))
+        self.lib.check(self.lib.dll.hb_p1function_download(self.h, level, as_dp(out)))
+        return out
+
+    def device_ptr(self, level):
+        return self.lib.dll.hb_p1function_device_ptr(self.h, level)
+
+    def _handles(self, fns):
+        arr = (C.c_void_p * len(fns))(*[f.h for f in fns])
+        return arr
+
+    def assign(self, scalars, functions, level, flag=All):
+        s = f64(scalars)
+        self.lib.check(self.lib.dll.hb_p1function_assign(self.h, len(functions), as_dp(s), self._handles(functions), level, flag))
+
+    def add(self, scalars, *args):
+        """add( scalars, functions, level, flag=All )  or  add( scalar, level, flag=All )"""
+        if np.isscalar(scalars):
+            level = args[0]
+            flag = args[1] if len(args) > 1 else All
+            self.lib.check(self.lib.dll.hb_p1function_add_scalar(self.h, float(scalars), level, flag))
+            return
+        functions, level = args[0], args[1]
+        flag = args[2] if len(args) > 2 else All
+        s = f64(scalars)
+        self.lib.check(self.lib.dll.hb_p1function_add(self.h, len(functions), as_dp(s), self._handles(functions), level, flag))
+
+    def multElementwise(self, functions, level, flag=All):
+        self.lib.check(self.lib.dll.hb_p1function_mult_elementwise(self.h, len(functions), self._handles(functions), level, flag))
+
+    def dotGlobal(self, other, level, flag=All):
+        out = C.c_double()
+        self.lib.check(self.lib.dll.hb_p1function_dot(self.h, other.h, level, flag, C.byref(out)))
+        return out.value
+
+    def sumGlobal(self, level, flag=All):
+        out = C.c_double()
+        self.lib.check(self.lib.dll.hb_p1function_sum(self.h, level, flag, C.byref(out)))
+        return out.value
+
+    def getMaxDoFMagnitude(self, level, flag=All):
+        out = C.c_double()
+        self.lib.check(self.lib.dll.hb_p1function_max_magnitude(self.h, level, flag, C.byref(out)))
+        return out.value
+
+
+class P1ConstantLaplaceOperator:
+    def __init__(self, storage, min_level, max_level):
+        self.storage, self.lib = storage, storage.lib
+        self.min_level, self.max_level = min_level, max_level
+        self.h = self.lib.checkp(self.lib.dll.hb_p1_constant_laplace_create(storage.h, min_level, max_level))
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.lib.dll.hb_operator_destroy(self.h)
+            self.h = None
+
+    def apply(self, src, dst, level, flag, update_type=Replace):
+        self.lib.check(self.lib.dll.hb_operator_apply(self.h, src.h, dst.h, level, flag, update_type))
+
+    def smooth_jac(self, dst, rhs, src, relax, level, flag):
+        self.lib.check(self.lib.dll.hb_operator_smooth_jac(self.h, dst.h, rhs.h, src.h, relax, level, flag))
+
+    def smooth_sor(self, dst, rhs, relax, level, flag, backwards=False):
+        self.lib.check(self.lib.dll.hb_operator_smooth_sor(self.h, dst.h, rhs.h, relax, level, flag, int(backwards)))
+
+    def smooth_gs(self, dst, rhs, level, flag):
+        self.smooth_sor(dst, rhs, 1.0, level, flag)
+
+    def residual(self, x, b, r, level, flag):
+        self.lib.check(self.lib.dll.hb_operator_residual(self.h, x.h, b.h, r.h, level, flag))
+
+    def cheb_first(self, x, b, dst, level, flag):
+        self.lib.check(self.lib.dll.hb_operator_cheb_first(self.h, x.h, b.h, dst.h, level, flag))
+
+    def cheb_step(self, src, dst, x, coeff, level, flag):
+        self.lib.check(self.lib.dll.hb_operator_cheb_step(self.h, src.h, dst.h, x.h, coeff, level, flag))
+
+    def diagonal(self, f, level, inverse=False):
+        self.lib.check(self.lib.dll.hb_operator_diagonal(self.h, f.h, level, int(inverse)))
+
+    def cell_stencil(self, level, local_cell, mask=0):
+        w = np.zeros(15)
+        self.lib.check(self.lib.dll.hb_operator_cell_stencil(self.h, level, local_cell, mask, as_dp(w)))
+        return w
+
+
+class P1toP1LinearRestriction:
+    def restrict(self, function, source_level, flag):
+        function.lib.check(function.lib.dll.hb_p1_restrict(function.h, source_level, flag))
+
+
+class P1toP1LinearProlongation:
+    def prolongate(self, function, source_level, flag):
+        function.lib.check(function.lib.dll.hb_p1_prolongate(function.h, source_level, flag))
+
+    def prolongateAndAdd(self, function, source_level, flag):
+        function.lib.check(function.lib.dll.hb_p1_prolongate_and_add(function.h, source_level, flag))
+
+
+class Solver:
+    def __init__(self, lib, handle, keep=()):
+        self.lib, self.h, self._keep = lib, lib.checkp(handle), keep
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.lib.dll.hb_solver_destroy(self.h)
+            self.h = None
+
+    def solve(self, A, x, b, level):
+        self.lib.check(self.lib.dll.hb_solver_solve(self.h, A.h, x.h, b.h, level))
+
+
+class CGSolver(Solver):
+    def __init__(self, storage, min_level, max_level, max_iter=-1, rel_tol=1e-16, abs_tol=1e-16):
+        super().__init__(storage.lib, storage.lib.dll.hb_solver_create_cg(storage.h, min_level, max_level, max_iter, rel_tol, abs_tol), (storage,))
+
+    def iterations(self):
+        return self.lib.dll.hb_solver_iterations(self.h)
+
+
+class WeightedJacobiSmoother(Solver):
+    def __init__(self, storage, min_level, max_level, relax):
+        super().__init__(storage.lib, storage.lib.dll.hb_solver_create_weighted_jacobi(storage.h, min_level, max_level, relax), (storage,))
+
+
+class SORSmoother(Solver):
+    def __init__(self, storage, relax):
+        super().__init__(storage.lib, storage.lib.dll.hb_solver_create_sor(relax), (storage,))
+
+
+class GaussSeidelSmoother(Solver):
+    def __init__(self, storage):
+        super().__init__(storage.lib, storage.lib.dll.hb_solver_create_gauss_seidel(), (storage,))
+
+
+class SymmetricGaussSeidelSmoother(Solver):
+    def __init__(self, storage):
+        super().__init__(storage.lib, storage.lib.dll.hb_solver_create_symmetric_gauss_seidel(), (storage,))
+
+
+class ChebyshevSmoother(Solver):
+    def __init__(self, storage, min_level, max_level):
+        super().__init__(storage.lib, storage.lib.dll.hb_solver_create_chebyshev(storage.h, min_level, max_level), (storage,))
+
+    def setupCoefficients(self, order, spectral_radius, upper_factor=1.2, lower_factor=0.3):
+        self.setupCoefficientsInternal(order, lower_factor * spectral_radius, upper_factor * spectral_radius)
+
+    def setupCoefficientsInternal(self, order, lower, upper):
+        self.lib.check(self.lib.dll.hb_chebyshev_setup_coefficients(self.h, order, lower, upper))
+
+    def coefficients(self):
+        c = np.zeros(64)
+        n = C.c_int()
+        self.lib.check(self.lib.dll.hb_chebyshev_coefficients(self.h, as_dp(c), C.byref(n)))
+        return c[: n.value].copy()
+
+
+def estimateRadius(A, level, max_iter, x, tmp):
+    """chebyshev::estimateRadius: power iteration on D^-1 A (x is the start vector, overwritten)."""
+    out = C.c_double()
+    A.lib.check(A.lib.dll.hb_estimate_spectral_radius(A.h, x.h, tmp.h, max_iter, level, C.byref(out)))
+    return out.value
+
+
+class GeometricMultigridSolver(Solver):
+    def __init__(self, storage, smoother, coarse_solver, min_level, max_level, pre=3, post=3, increment=0, cycle=VCYCLE):
+        super().__init__(storage.lib, storage.lib.dll.hb_solver_create_gmg(
+            storage.h, smoother.h, coarse_solver.h, min_level, max_level, pre, post, increment, cycle),
+            (storage, smoother, coarse_solver))

@@ -95,6 +95,7 @@ struct HbStencilArgs
    int32_t              colour;  // SOR colour 0..3 (interior)
    int32_t              dimSel;  // boundary phase: bitmask of primitive dims to process (1<<dim)
    int32_t              toScratch; // boundary results go to scratch instead of dst
+   int32_t              bndColour; // interface colour to process (-1: all), see hb_interface_colour
    HbBC                 bc;
 };
 
@@ -174,4 +175,33 @@ __device__ __forceinline__ void hb_boundary_stencil( const HbLevelView&   lv,
       sNb += part;
       diag += w[0];
    }
+}
+
+// Colour of an interface point inside its macro primitive, identical in every macro-cell that holds
+// a copy: the barycentric weights are taken w.r.t. the primitive's macro vertices sorted by global id.
+//   macro vertex: 0 ; macro edge: parity of the position along the edge (2 colours);
+//   macro face: (b1 + 2 b2) mod 3, a proper 3-colouring of the triangular lattice.
+__device__ __forceinline__ int hb_interface_colour( const HbCellInfo& ci, int N, int x, int y, int z )
+{
+   const int b[4] = { N - x - y - z, x, y, z };
+   int       idx[4];
+   int       n = 0;
+#pragma unroll
+   for ( int j = 0; j < 4; j++ )
+      if ( b[j] != 0 )
+      {
+         // insertion sort by global vertex id
+         int k = n++;
+         while ( k > 0 && ci.gv[idx[k - 1]] > ci.gv[j] )
+         {
+            idx[k] = idx[k - 1];
+            k--;
+         }
+         idx[k] = j;
+      }
+   if ( n == 2 )
+      return b[idx[1]] & 1;
+   if ( n == 3 )
+      return ( b[idx[1]] + 2 * b[idx[2]] ) % 3;
+   return 0;
 }

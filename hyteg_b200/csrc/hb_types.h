@@ -41,6 +41,7 @@ struct HbCellInfo
    int32_t  copyEnd;
    int32_t  globalId;
    int32_t  pad;
+   int32_t  gv[4]; // global macro-vertex ids of the local vertices (canonical interface colouring)
 };
 
 // One entry of a macro-cell's copy list: a macro-cell (slot index into the cell pointer table)

@@ -135,6 +135,8 @@ __device__ __forceinline__ void hb_boundary_item( const HbLevelView& lv, const H
       return;
    if ( !( ( a.dimSel >> reg.dim ) & 1 ) )
       return;
+   if ( a.bndColour >= 0 && hb_interface_colour( lv.cells[cell], lv.N, p.x, p.y, p.z ) != a.bndColour )
+      return;
    double sNb, diag;
    hb_boundary_stencil( lv, a.W, a.src, cell, p.x, p.y, p.z, sNb, diag );
    const size_t gi     = (size_t) cell * lv.cellSize + hb_index( lv.N, p.x, p.y, p.z );
@@ -177,6 +179,8 @@ __global__ void hb_commit_kernel( const HbLevelView lv, const HbStencilArgs a )
    if ( !( a.bc.type[reg.bflag] & a.flag ) )
       return;
    if ( !( ( a.dimSel >> reg.dim ) & 1 ) )
+      return;
+   if ( a.bndColour >= 0 && hb_interface_colour( lv.cells[cell], lv.N, p.x, p.y, p.z ) != a.bndColour )
       return;
    a.dst[(size_t) cell * lv.cellSize + hb_index( lv.N, p.x, p.y, p.z )] = a.scratch[item];
 }

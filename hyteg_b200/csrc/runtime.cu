@@ -1,0 +1,359 @@
+// C-ABI implementation, part 1: runtime, PrimitiveStorage tables, P1Function storage and BLAS-1.
+#include "runtime.hpp"
+
+#include <cstring>
+
+#include "../../include/hyteg_b200.h"
+#include "stencil_assembly.hpp"
+
+namespace hb {
+
+static thread_local std::string g_lastError;
+static cudaStream_t             g_stream = 0;
+static std::map< std::string, int > g_tuning;
+hb_allreduce_fn                 g_allreduce    = nullptr;
+void*                           g_allreduceCtx = nullptr;
+
+void setError( const std::string& s )
+{
+   g_lastError = s;
+}
+
+void cudaCheck( cudaError_t e, const char* what )
+{
+   if ( e != cudaSuccess )
+      throw std::runtime_error( std::string( "hyteg_b200: CUDA error in " ) + what + ": " + cudaGetErrorString( e ) );
+}
+
+cudaStream_t currentStream()
+{
+   return g_stream;
+}
+
+int tuning( const std::string& key, int dflt )
+{
+   auto it = g_tuning.find( key );
+   return it == g_tuning.end() ? dflt : it->second;
+}
+
+} // namespace hb
+
+using namespace hb;
+
+#define HB_TRY try {
+#define HB_CATCH( ret )                   \
+   }                                      \
+   catch ( const std::exception& e )      \
+   {                                      \
+      hb::setError( e.what() );           \
+      return ret;                         \
+   }
+
+static void require( bool cond, const char* msg )
+{
+   if ( !cond )
+      throw std::runtime_error( std::string( "hyteg_b200: " ) + msg );
+}
+
+// ------------------------------------------------------------------------------------------------
+// storage
+// ------------------------------------------------------------------------------------------------
+
+hb_storage::~hb_storage()
+{
+   if ( hReduce )
+      cudaFreeHost( hReduce );
+}
+
+void hb_storage::uploadTopologyTables()
+{
+   view.build( topo, view.rank, view.nRanks );
+   dCells.upload( view.cells );
+   dCopies.upload( view.copies );
+   for ( auto& kv : levels )
+   {
+      kv.second->view.cells  = dCells.ptr;
+      kv.second->view.copies = dCopies.ptr;
+      kv.second->view.nSlots = (int) view.slotGlobal.size();
+   }
+   tablesDirty = false;
+}
+
+hb::LevelTables& hb_storage::level( int L )
+{
+   if ( tablesDirty )
+      uploadTopologyTables();
+   auto it = levels.find( L );
+   if ( it != levels.end() )
+      return *it->second;
+   require( L >= 0 && L <= 10, "level out of range [0,10]" );
+   auto      lt = std::make_unique< hb::LevelTables >();
+   const int N  = 1 << L;
+   std::vector< HbBndPoint > bnd;
+   std::vector< uint8_t >    mask;
+   lt->hXyz.clear();
+   for ( int z = 0; z <= N; z++ )
+      for ( int y = 0; y <= N - z; y++ )
+         for ( int x = 0; x <= N - z - y; x++ )
+         {
+            HbBndPoint p;
+            p.x    = (uint16_t) x;
+            p.y    = (uint16_t) y;
+            p.z    = (uint16_t) z;
+            p.mask = (uint16_t) hb_mask( N, x, y, z );
+            require( (size_t) hb_index( N, x, y, z ) == lt->hXyz.size(), "internal: macro-cell index layout mismatch" );
+            lt->hXyz.push_back( p );
+            mask.push_back( (uint8_t) p.mask );
+            if ( p.mask )
+               bnd.push_back( p );
+         }
+   const int tileRows = hb::tuning( "tile_rows", 16 );
+   const int wpb      = 8;
+   std::vector< HbTile > tiles;
+   for ( int z0 = 1; z0 <= N - 3; z0 += wpb )
+      for ( int y0 = 1; y0 <= N - 2 - z0; y0 += tileRows )
+         for ( int x0 = 1; x0 <= N - 1 - y0 - z0; x0 += 32 )
+         {
+            HbTile t;
+            t.z0  = (int16_t) z0;
+            t.y0  = (int16_t) y0;
+            t.x0  = (int16_t) x0;
+            t.pad = 0;
+            tiles.push_back( t );
+         }
+   lt->bnd.upload( bnd );
+   lt->xyz.upload( lt->hXyz );
+   lt->mask.upload( mask );
+   lt->tiles.upload( tiles );
+   lt->scratch.alloc( (size_t) view.nLocal * bnd.size() );
+   HbLevelView& v = lt->view;
+   v.level        = L;
+   v.N            = N;
+   v.cellSize     = (int) lt->hXyz.size();
+   v.nCells       = view.nLocal;
+   v.nSlots       = (int) view.slotGlobal.size();
+   v.nBnd         = (int) bnd.size();
+   v.nTiles       = (int) tiles.size();
+   v.tileRows     = tileRows;
+   v.bnd          = lt->bnd.ptr;
+   v.mask         = lt->mask.ptr;
+   v.xyz          = lt->xyz.ptr;
+   v.tiles        = lt->tiles.ptr;
+   v.cells        = dCells.ptr;
+   v.copies       = dCopies.ptr;
+   auto& ref      = *lt;
+   levels[L]      = std::move( lt );
+   return ref;
+}
+
+extern "C" {
+
+const char* hb_last_error( void )
+{
+   return hb::g_lastError.c_str();
+}
+
+const char* hb_version( void )
+{
+#ifdef HB_EMUL
+   return "hyteg_b200 0.1 (HOST EMULATION - tests only)";
+#else
+   return "hyteg_b200 0.1 (sm_100a)";
+#endif
+}
+
+int hb_device_init( int device )
+{
+   HB_TRY
+#ifndef HB_EMUL
+   int n = 0;
+   cudaCheck( cudaGetDeviceCount( &n ), "cudaGetDeviceCount" );
+   require( n > 0, "no CUDA device: hyteg_b200 has no CPU fallback" );
+#endif
+   cudaCheck( cudaSetDevice( device ), "cudaSetDevice" );
+   return 0;
+   HB_CATCH( 1 )
+}
+
+int hb_set_stream( void* s )
+{
+   hb::g_stream = (cudaStream_t) s;
+   return 0;
+}
+
+int hb_synchronize( void )
+{
+   HB_TRY
+   cudaCheck( cudaStreamSynchronize( hb::g_stream ), "cudaStreamSynchronize" );
+   return 0;
+   HB_CATCH( 1 )
+}
+
+int hb_set_allreduce( hb_allreduce_fn fn, void* ctx )
+{
+   hb::g_allreduce    = fn;
+   hb::g_allreduceCtx = ctx;
+   return 0;
+}
+
+int hb_set_tuning( const char* key, int value )
+{
+   hb::g_tuning[key] = value;
+   return 0;
+}
+
+hb_storage* hb_storage_create( int nV, const double* xyz, int nC, const int* cells, int rank, int nRanks )
+{
+   HB_TRY
+   require( nRanks >= 1 && rank >= 0 && rank < nRanks, "bad rank / n_ranks" );
+   auto st = std::make_unique< hb_storage >();
+   st->topo.build( nV, xyz, nC, cells );
+   st->topo.partition( nRanks );
+   st->view.rank   = rank;
+   st->view.nRanks = nRanks;
+   st->reducePartial.alloc( HB_REDUCE_MAX_BLOCKS );
+   st->reduceOut.alloc( 8 );
+   cudaCheck( cudaMallocHost( (void**) &st->hReduce, 8 * sizeof( double ) ), "cudaMallocHost" );
+   st->uploadTopologyTables();
+   return st.release();
+   HB_CATCH( nullptr )
+}
+
+void hb_storage_destroy( hb_storage* st )
+{
+   delete st;
+}
+
+int hb_storage_set_mesh_boundary_flags_on_boundary( hb_storage* st, int fb, int fi, int highestDimAlwaysInner )
+{
+   HB_TRY
+   require( fb >= 0 && fb < 16 && fi >= 0 && fi < 16, "mesh boundary flags must be in [0,15]" );
+   st->topo.setMeshBoundaryFlagsOnBoundary( fb, fi, highestDimAlwaysInner != 0 );
+   st->tablesDirty = true;
+   return 0;
+   HB_CATCH( 1 )
+}
+
+int hb_storage_counts( const hb_storage* st, int* c )
+{
+   c[0] = st->topo.nV;
+   c[1] = st->topo.nE;
+   c[2] = st->topo.nF;
+   c[3] = st->topo.nC;
+   return 0;
+}
+
+int hb_storage_primitive_vertices( const hb_storage* st, int dim, int* out )
+{
+   HB_TRY
+   const hb::Topology& t = st->topo;
+   switch ( dim )
+   {
+   case 0:
+      for ( int i = 0; i < t.nV; i++ )
+         out[i] = i;
+      break;
+   case 1:
+      for ( int i = 0; i < t.nE; i++ )
+         for ( int k = 0; k < 2; k++ )
+            out[2 * i + k] = t.edgeV[i][k];
+      break;
+   case 2:
+      for ( int i = 0; i < t.nF; i++ )
+         for ( int k = 0; k < 3; k++ )
+            out[3 * i + k] = t.faceV[i][k];
+      break;
+   case 3:
+      for ( int i = 0; i < t.nC; i++ )
+         for ( int k = 0; k < 4; k++ )
+            out[4 * i + k] = t.cellV[i][k];
+      break;
+   default:
+      require( false, "dim must be 0..3" );
+   }
+   return 0;
+   HB_CATCH( 1 )
+}
+
+static std::vector< int >& flagsOf( hb::Topology& t, int dim )
+{
+   require( dim >= 0 && dim <= 3, "dim must be 0..3" );
+   return dim == 0 ? t.vFlag : dim == 1 ? t.eFlag : dim == 2 ? t.fFlag : t.cFlag;
+}
+
+int hb_storage_get_mesh_boundary_flags( const hb_storage* st, int dim, int* out )
+{
+   HB_TRY
+   auto& f = flagsOf( const_cast< hb::Topology& >( st->topo ), dim );
+   std::memcpy( out, f.data(), f.size() * sizeof( int ) );
+   return 0;
+   HB_CATCH( 1 )
+}
+
+int hb_storage_set_mesh_boundary_flags( hb_storage* st, int dim, const int* in )
+{
+   HB_TRY
+   auto& f = flagsOf( st->topo, dim );
+   for ( size_t i = 0; i < f.size(); i++ )
+   {
+      require( in[i] >= 0 && in[i] < 16, "mesh boundary flags must be in [0,15]" );
+      f[i] = in[i];
+   }
+   st->tablesDirty = true;
+   return 0;
+   HB_CATCH( 1 )
+}
+
+int hb_storage_num_local_cells( const hb_storage* st )
+{
+   return st->view.nLocal;
+}
+
+int hb_storage_local_cell_global_id( const hb_storage* st, int l )
+{
+   return ( l >= 0 && l < st->view.nLocal ) ? st->view.slotGlobal[l] : -1;
+}
+
+long long hb_cell_array_size( int level )
+{
+   const long long w = ( 1LL << level ) + 1;
+   return w * ( w + 1 ) * ( w + 2 ) / 6;
+}
+
+long long hb_storage_num_global_dofs( const hb_storage* st, int level )
+{
+   const long long     N = 1LL << level;
+   const hb::Topology& t = st->topo;
+   const long long     e = N - 1;
+   const long long     f = N >= 3 ? ( N - 1 ) * ( N - 2 ) / 2 : 0;
+   const long long     c = N >= 4 ? ( N - 1 ) * ( N - 2 ) * ( N - 3 ) / 6 : 0;
+   return t.nV + e * t.nE + f * t.nF + c * t.nC;
+}
+
+int hb_storage_micro_coordinates( const hb_storage* cst, int level, double* xyz )
+{
+   HB_TRY
+   hb_storage*         st = const_cast< hb_storage* >( cst );
+   hb::LevelTables&    lt = st->level( level );
+   const hb::Topology& t  = st->topo;
+   const double        h  = 1.0 / (double) lt.view.N;
+   size_t              o  = 0;
+   for ( int l = 0; l < st->view.nLocal; l++ )
+   {
+      const int g = st->view.slotGlobal[l];
+      double    v[4][3];
+      for ( int j = 0; j < 4; j++ )
+         for ( int k = 0; k < 3; k++ )
+            v[j][k] = t.xyz[3 * t.cellV[g][j] + k];
+      for ( const HbBndPoint& p : lt.hXyz )
+         for ( int k = 0; k < 3; k++ )
+            xyz[o++] = v[0][k] + h * ( p.x * ( v[1][k] - v[0][k] ) + p.y * ( v[2][k] - v[0][k] ) + p.z * ( v[3][k] - v[0][k] ) );
+   }
+   return 0;
+   HB_CATCH( 1 )
+}
+
+} // extern "C"
+
+#include "runtime_function.inc"
+#include "runtime_operator.inc"

@@ -1,0 +1,98 @@
+// Host runtime objects behind the C-ABI handles.
+#pragma once
+#include <map>
+#include <memory>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "hb_compat.h"
+#include "hb_device.h"
+#include "kernels.h"
+#include "topology.hpp"
+
+namespace hb {
+
+void         cudaCheck( cudaError_t e, const char* what );
+cudaStream_t currentStream();
+int          tuning( const std::string& key, int dflt );
+
+template < typename T >
+struct DeviceBuffer
+{
+   T*     ptr = nullptr;
+   size_t n   = 0;
+   DeviceBuffer() {}
+   DeviceBuffer( const DeviceBuffer& )            = delete;
+   DeviceBuffer& operator=( const DeviceBuffer& ) = delete;
+   ~DeviceBuffer() { release(); }
+   void release()
+   {
+      if ( ptr )
+         cudaFree( ptr );
+      ptr = nullptr;
+      n   = 0;
+   }
+   void alloc( size_t count )
+   {
+      release();
+      n = count;
+      cudaCheck( cudaMalloc( (void**) &ptr, ( count ? count : 1 ) * sizeof( T ) ), "cudaMalloc" );
+   }
+   void upload( const std::vector< T >& h )
+   {
+      alloc( h.size() );
+      if ( !h.empty() )
+         cudaCheck( cudaMemcpy( ptr, h.data(), h.size() * sizeof( T ), cudaMemcpyHostToDevice ), "cudaMemcpy H2D" );
+   }
+};
+
+struct LevelTables
+{
+   HbLevelView                view{};
+   DeviceBuffer< HbBndPoint > bnd, xyz;
+   DeviceBuffer< uint8_t >    mask;
+   DeviceBuffer< HbTile >     tiles;
+   DeviceBuffer< double >     scratch; // nCells*nBnd, interface staging (SOR)
+   std::vector< HbBndPoint >  hXyz;    // host copy of the coordinate template
+};
+
+} // namespace hb
+
+struct hb_storage
+{
+   hb::Topology                             topo;
+   hb::LocalView                            view;
+   hb::DeviceBuffer< HbCellInfo >           dCells;
+   hb::DeviceBuffer< HbCopy >               dCopies;
+   std::map< int, std::unique_ptr< hb::LevelTables > > levels;
+   hb::DeviceBuffer< double >               reducePartial; // HB_REDUCE_MAX_BLOCKS
+   hb::DeviceBuffer< double >               reduceOut;     // 8 slots
+   double*                                  hReduce = nullptr; // pinned
+   bool                                     tablesDirty = true;
+
+   hb::LevelTables& level( int L );
+   void             uploadTopologyTables();
+   ~hb_storage();
+};
+
+struct hb_function
+{
+   hb_storage* st;
+   int         minLevel, maxLevel;
+   HbBC        bc;
+   std::vector< hb::DeviceBuffer< double > >  data;    // per level: local arena
+   std::vector< hb::DeviceBuffer< double* > > cellPtr; // per level: [nSlots] device pointers
+   double*        arena( int L ) const;
+   double* const* ptrs( int L ) const;
+   void           check( int L ) const;
+};
+
+struct hb_operator
+{
+   hb_storage* st;
+   int         minLevel, maxLevel;
+   std::vector< hb::DeviceBuffer< double > > W;  // per level [nSlots][16][15]
+   std::vector< std::vector< double > >      hW; // host copy
+   const double* weights( int L ) const;
+};

@@ -198,6 +198,8 @@ void LocalView::build( const Topology& topo, int rank_, int nRanks_ )
    copies.clear();
    auto fillRegions = [&topo]( HbCellInfo& ci, int c ) {
       ci.globalId = c;
+      for ( int j = 0; j < 4; j++ )
+         ci.gv[j] = topo.cellV[c][j];
       for ( int m = 0; m < 16; m++ )
       {
          int dim, id;

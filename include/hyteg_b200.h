@@ -85,6 +85,9 @@ hb_function* hb_p1function_create( hb_storage* st, int min_level, int max_level 
 void         hb_p1function_destroy( hb_function* f );
 /* BoundaryCondition: meshBoundaryFlag -> DoFType; default create0123BC (0 Inner,1 Dirichlet,2 Neumann,3 Freeslip) */
 int hb_p1function_set_boundary_condition( hb_function* f, const int* dof_type_of_flag, int n );
+int hb_p1function_copy_boundary_condition( hb_function* dst, const hb_function* src ); /* copyBCs */
+hb_storage* hb_p1function_storage( const hb_function* f );
+int hb_p1function_level_range( const hb_function* f, int* min_level, int* max_level );
 /* Whole local arena (n_local_cells * cell_array_size doubles, macro-cell after macro-cell, each in
  * HyTeG's macro-cell layout, src/hyteg/indexing/MacroCellIndexing.hpp:44-52).  Only DoFs whose
  * primitive matches 'flag' are written (interpolate semantics, VertexDoFFunction.cpp interpolate). */
@@ -111,6 +114,7 @@ int hb_p1function_max_magnitude( const hb_function* a, int level, int flag, doub
  *      src/hyteg/p1functionspace/P1Operator.hpp:192-447, src/hyteg/operators/Operator.hpp:76-83) ---- */
 hb_operator* hb_p1_constant_laplace_create( hb_storage* st, int min_level, int max_level );
 void         hb_operator_destroy( hb_operator* op );
+int          hb_operator_level_range( const hb_operator* op, int* min_level, int* max_level );
 /* Operator::apply( src, dst, level, flag, updateType ) */
 int hb_operator_apply( hb_operator* op, const hb_function* src, hb_function* dst, int level, int flag, int update_type );
 /* P1Operator::smooth_jac( dst, rhs, src, omega, level, flag )  (P1Operator.hpp:429-447), one fused kernel */
