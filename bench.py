@@ -1,0 +1,264 @@
+"""bench.py -- P1 constant-stencil apply throughput (GDoF/s) on cube_6el level 8, with roofline, V(3,3) time,
+end-to-end (host buffers through the C-ABI) and the reference's CPU kernels as baseline.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--level L] [--impl ours|reference]
+  torchrun --nproc-per-node N bench.py --gpus N ...      (one rank per GPU)
+
+One "step" = one Operator::apply(src, dst, level, Inner) over the whole mesh.  See DESIGN.md (Measurement).
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+BYTES_PER_DOF = {"apply": 16.0, "jacobi": 24.0, "sor": 24.0}  # algorithmic: src+dst / src+rhs+dst
+
+
+def parse():
+    p = argparse.ArgumentParser()
+    p.add_argument("--gpus", type=int, default=1)
+    p.add_argument("--steps", type=int, default=50)
+    p.add_argument("--warmup", type=int, default=5)
+    p.add_argument("--level", type=int, default=8)
+    p.add_argument("--impl", default="ours")
+    p.add_argument("--no-cpu-baseline", action="store_true")
+    return p.parse_args()
+
+
+def measured_peak():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+class ClockSampler:
+    """samples SM clock + throttle reasons through NVML during the timed region"""
+
+    def __init__(self, index):
+        self.samples, self.reasons, self.stop_flag, self.max_mhz = [], set(), False, None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+        self.t = threading.Thread(target=self.run, daemon=True)
+
+    def run(self):
+        nv = self.nv
+        names = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
+        while not self.stop_flag:
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h) if hasattr(nv, "nvmlDeviceGetCurrentClocksEventReasons") \
+                    else nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, n in names.items():
+                    if r & bit:
+                        self.reasons.add(n)
+            except Exception:
+                pass
+            time.sleep(0.02)
+
+    def __enter__(self):
+        if self.nv:
+            self.t.start()
+        return self
+
+    def __exit__(self, *a):
+        self.stop_flag = True
+        if self.nv:
+            self.t.join()
+
+    def summary(self):
+        return {"sm_mhz": float(np.median(self.samples)) if self.samples else None, "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons)}
+
+
+# ------------------------------------------------------------------------------------------------
+# reference arm / cpu baseline: the reference's own generated macro-cell apply kernel (oracle/_ref)
+# ------------------------------------------------------------------------------------------------
+def cpu_reference_apply(level, n_cells=6, repeats=3, threads=None):
+    """Times apply_3D_macrocell_vertexdof_to_vertexdof_replace (compiled from the reference tree into
+    oracle/_ref) on n_cells macro-cells of `level`, one thread per macro-cell (the reference parallelises
+    over macro-primitives).  Only the macro-cell kernel is timed: the reference's macro-face/edge/vertex
+    kernels and ghost-layer copies (~36 % of its apply) are left out, which favours the CPU."""
+    import ctypes as C
+    so = os.path.join(ROOT, "oracle", "_ref", "libhyteg_ref_kernels.so")
+    if not os.path.exists(so):
+        return None
+    dll = C.CDLL(so)
+    dp = C.POINTER(C.c_double)
+    dll.ref_apply_macrocell.argtypes = [dp, dp, C.c_int, dp, C.c_int]
+    n = (2 ** level + 1) * (2 ** level + 2) * (2 ** level + 3) // 6
+    N = 2 ** level
+    interior = (N - 1) * (N - 2) * (N - 3) // 6
+    threads = threads or min(n_cells, os.cpu_count() or 1)
+    rng = np.random.default_rng(0)
+    src = [rng.standard_normal(n) for _ in range(n_cells)]
+    dst = [np.zeros(n) for _ in range(n_cells)]
+    w = np.array([8.0] + [-0.5] * 14)
+
+    def work(i):
+        dll.ref_apply_macrocell(dst[i].ctypes.data_as(dp), src[i].ctypes.data_as(dp), level, w.ctypes.data_as(dp), 0)
+
+    def sweep():
+        ts = []
+        for base in range(0, n_cells, threads):
+            ts = [threading.Thread(target=work, args=(i,)) for i in range(base, min(base + threads, n_cells))]
+            [t.start() for t in ts]
+            [t.join() for t in ts]
+
+    sweep()
+    best = 1e30
+    for _ in range(repeats):
+        t0 = time.perf_counter()
+        sweep()
+        best = min(best, time.perf_counter() - t0)
+    return {"value": interior * n_cells / best / 1e9, "unit": "GDoF/s", "cores": threads, "kind": "reference",
+            "sample": f"reference macro-cell apply kernel only, {n_cells} macro-cells at level {level}, best of {repeats}",
+            "seconds": best}
+
+
+def run_reference(args, rank):
+    if rank != 0:
+        return
+    t0 = time.perf_counter()
+    vals = []
+    base = None
+    for _ in range(max(1, min(args.steps, 5)) + min(args.warmup, 1)):
+        base = cpu_reference_apply(args.level, repeats=1)
+        if base is None:
+            print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref not built (needs /root/reference at build time)"}))
+            return
+        vals.append(base["value"])
+        if time.perf_counter() - t0 > 120:
+            break
+    v = float(np.max(vals))
+    base["value"] = v
+    line = {"impl": "reference", "metric": "P1 constant-stencil apply throughput", "value": v, "unit": "GDoF/s", "n_gpus": args.gpus,
+            "steps": len(vals), "warmup": 0, "ms_per_step": 1e3 * base.pop("seconds"), "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": f"cube_6el level {args.level} P1 Laplace constant-stencil apply (CPU reference kernels)"},
+            "cpu_baseline": base, "e2e": {"value": v, "unit": "GDoF/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+def main():
+    args = parse()
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    if args.impl == "reference":
+        run_reference(args, rank)
+        return
+
+    import torch
+    import torch.distributed as dist
+    import hyteg_b200 as hb
+    from hyteg_b200 import api, meshes
+
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    lib = hb.get_lib()
+    lib.check(lib.dll.hb_device_init(local))
+    stream = torch.cuda.current_stream()
+    lib.check(lib.dll.hb_set_stream(stream.cuda_stream))
+
+    L = args.level
+    v, c = meshes.cube_6el()
+    # N > 1: every rank works on its own cube_6el replica (weak scaling, no data-path collective yet)
+    st = api.PrimitiveStorage(v, c)
+    st.setMeshBoundaryFlagsOnBoundary(1, 0, True)
+    A = api.P1ConstantLaplaceOperator(st, 0, L)
+    src, dst, rhs = (api.P1Function(n, st, 0, L) for n in ("src", "dst", "rhs"))
+    n_arr = st.num_local_cells * st.cell_array_size(L)
+    ndof = st.num_global_dofs(L)
+    host = torch.empty(n_arr, dtype=torch.float64).pin_memory()
+    host.copy_(torch.from_numpy(np.random.default_rng(rank).standard_normal(n_arr)))
+    hout = torch.empty(n_arr, dtype=torch.float64).pin_memory()
+    hp = host.data_ptr()
+    import ctypes as C
+    dp = C.POINTER(C.c_double)
+    lib.check(lib.dll.hb_p1function_upload(src.h, L, C.cast(hp, dp), hb.All))
+    lib.check(lib.dll.hb_p1function_upload(rhs.h, L, C.cast(hp, dp), hb.All))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps, warmup):
+        for _ in range(warmup):
+            fn()
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(steps):
+            fn()
+        e1.record(stream)
+        barrier()
+        ms = e0.elapsed_time(e1)
+        if world > 1:
+            t = torch.tensor([ms], device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms / steps
+
+    smooth = hb.SMOOTH_FLAG
+    W = max(args.warmup, 3)
+    with ClockSampler(local) as clk:
+        ms_apply = timed(lambda: A.apply(src, dst, L, hb.Inner), args.steps, W)
+    ms_jac = timed(lambda: A.smooth_jac(dst, rhs, src, 0.66, L, smooth), args.steps, W)
+    ms_sor = timed(lambda: A.smooth_sor(dst, rhs, 1.0, L, smooth), max(args.steps // 5, 2), 3)
+
+    # V(3,3) cycle, Gauss-Seidel smoother, CG on level 0
+    x, b = api.P1Function("x", st, 0, L), api.P1Function("b", st, 0, L)
+    x.interpolate(1.0, L, hb.DirichletBoundary)
+    gmg = api.GeometricMultigridSolver(st, api.GaussSeidelSmoother(st), api.CGSolver(st, 0, 0, 50, 1e-16, 1e-16), 0, L, 3, 3)
+    ms_v = timed(lambda: gmg.solve(A, x, b, L), max(args.steps // 10, 2), 2)
+
+    # end to end through the C-ABI with pinned HOST buffers: H2D src, apply, D2H dst
+    def e2e_step():
+        lib.check(lib.dll.hb_p1function_upload(src.h, L, C.cast(hp, dp), hb.All))
+        A.apply(src, dst, L, hb.Inner)
+        lib.check(lib.dll.hb_p1function_download(dst.h, L, C.cast(hout.data_ptr(), dp)))
+    ms_e2e = timed(e2e_step, max(args.steps // 5, 3), 3)
+
+    if rank == 0:
+        peak, which = measured_peak()
+        gd = lambda ms: world * ndof / (ms * 1e-3) / 1e9
+        achieved = BYTES_PER_DOF["apply"] * ndof / (ms_apply * 1e-3) / 1e9
+        line = {"metric": "P1 constant-stencil apply throughput", "value": gd(ms_apply), "unit": "GDoF/s", "n_gpus": world,
+                "steps": args.steps, "warmup": W, "ms_per_step": ms_apply, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                "config": {"workload": f"cube_6el level {L} P1 Laplace constant-stencil apply, {ndof} DoFs per GPU",
+                           "l2": "src+dst arrays %.0f MB > 126 MB L2" % (2 * 8 * n_arr / 1e6),
+                           "multi_gpu": "independent replicas per rank" if world > 1 else "single"},
+                "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                             "traffic": None, "peak_source": which, "kernel": "hb_stencil_kernel<APPLY_REPLACE>"},
+                "also": {"jacobi_gdofs": gd(ms_jac), "jacobi_frac": BYTES_PER_DOF["jacobi"] * ndof / (ms_jac * 1e-3) / 1e9 / peak,
+                         "sor_gdofs": gd(ms_sor), "sor_frac": BYTES_PER_DOF["sor"] * ndof / (ms_sor * 1e-3) / 1e9 / peak,
+                         "vcycle_3_3_gs_ms": ms_v},
+                "e2e": {"value": gd(ms_e2e), "unit": "GDoF/s", "h2d_bytes_per_step": 8 * n_arr, "d2h_bytes_per_step": 8 * n_arr},
+                "gpu_launches": args.steps, "clocks": clk.summary()}
+        if not args.no_cpu_baseline and world == 1:
+            line["cpu_baseline"] = cpu_reference_apply(min(L, 8), repeats=2)
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
