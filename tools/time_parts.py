@@ -1,0 +1,25 @@
+"""Times apply with interior only / interface only / both (tuning knob apply_parts) using CUDA events via torch."""
+import os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+import hyteg_b200 as hb
+from hyteg_b200 import api, meshes
+L = int(sys.argv[1]) if len(sys.argv) > 1 else 8
+lib = hb.get_lib(); lib.check(lib.dll.hb_device_init(0))
+s = torch.cuda.current_stream(); lib.dll.hb_set_stream(s.cuda_stream)
+v, c = meshes.cube_6el()
+st = api.PrimitiveStorage(v, c); st.setMeshBoundaryFlagsOnBoundary(1, 0, True)
+A = api.P1ConstantLaplaceOperator(st, L, L)
+src, dst = api.P1Function("s", st, L, L), api.P1Function("d", st, L, L)
+src.interpolate(1.0, L, hb.All)
+def t(fn, n=20):
+    for _ in range(3): fn()
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record(s)
+    for _ in range(n): fn()
+    b.record(s); torch.cuda.synchronize()
+    return a.elapsed_time(b) / n * 1e3
+for parts in (1, 2, 3):
+    lib.dll.hb_set_tuning(b"apply_parts", parts)
+    print("apply_parts", parts, "%.1f us" % t(lambda: A.apply(src, dst, L, hb.All)))
