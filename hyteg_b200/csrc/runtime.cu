@@ -125,6 +125,11 @@ hb::LevelTables& hb_storage::level( int L )
    lt->xyz.upload( lt->hXyz );
    lt->mask.upload( mask );
    lt->tiles.upload( tiles );
+   {
+      std::vector< HbItem > items;
+      hb_stream_build_items( N, items );
+      lt->items.upload( items );
+   }
    lt->scratch.alloc( (size_t) view.nLocal * bnd.size() );
    HbLevelView& v = lt->view;
    v.level        = L;
@@ -213,6 +218,8 @@ hb_storage* hb_storage_create( int nV, const double* xyz, int nC, const int* cel
    st->view.nRanks = nRanks;
    st->reducePartial.alloc( HB_REDUCE_MAX_BLOCKS );
    st->reduceOut.alloc( 8 );
+   st->workCounter.alloc( 2 );
+   cudaCheck( cudaMemset( st->workCounter.ptr, 0, 2 * sizeof( int32_t ) ), "cudaMemset" );
    cudaCheck( cudaMallocHost( (void**) &st->hReduce, 8 * sizeof( double ) ), "cudaMallocHost" );
    st->uploadTopologyTables();
    return st.release();

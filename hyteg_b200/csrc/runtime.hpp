@@ -9,6 +9,7 @@
 #include "hb_compat.h"
 #include "hb_device.h"
 #include "kernels.h"
+#include "stream_kernel.h"
 #include "topology.hpp"
 
 namespace hb {
@@ -53,6 +54,7 @@ struct LevelTables
    DeviceBuffer< HbBndPoint > bnd, xyz;
    DeviceBuffer< uint8_t >    mask;
    DeviceBuffer< HbTile >     tiles;
+   DeviceBuffer< HbItem >     items;   // work items of the streamed interior kernel
    DeviceBuffer< double >     scratch; // nCells*nBnd, interface staging (SOR)
    std::vector< HbBndPoint >  hXyz;    // host copy of the coordinate template
 };
@@ -68,6 +70,7 @@ struct hb_storage
    std::map< int, std::unique_ptr< hb::LevelTables > > levels;
    hb::DeviceBuffer< double >               reducePartial; // HB_REDUCE_MAX_BLOCKS
    hb::DeviceBuffer< double >               reduceOut;     // 8 slots
+   hb::DeviceBuffer< int32_t >              workCounter;   // [2] streamed-kernel work counters (zero between launches)
    double*                                  hReduce = nullptr; // pinned
    bool                                     tablesDirty = true;
 

@@ -106,3 +106,44 @@ def test_full_size_properties(cuda_lib):
     A.apply(w, t, L, Inner)
     a, b = r.dotGlobal(w, L, Inner), t.dotGlobal(u, L, Inner)
     assert abs(a - b) < 1e-11 * abs(a), (a, b)
+
+
+@pytest.mark.parametrize("name,L", [("cube_6el", 5), ("cube_6el", 6), ("regular_octahedron_8el", 5), ("tet_tilted_1el", 7)])
+def test_streamed_kernel_bit_identical_to_generic(cuda_lib, name, L):
+    """the TMA-streamed interior kernel uses the same operation order as the generic kernel: results must be bitwise equal
+    for every fused mode (apply replace/add, residual, Jacobi, Chebyshev first/step)"""
+    v, c = meshes.golden(name)
+    st = api.PrimitiveStorage(v, c, lib=cuda_lib)
+    st.setMeshBoundaryFlagsOnBoundary(1, 0, True)
+    A = api.P1ConstantLaplaceOperator(st, L, L)
+    n = st.num_local_cells * st.cell_array_size(L)
+    rng = np.random.default_rng(L)
+    f = {k: api.P1Function(k, st, L, L) for k in ("src", "rhs", "dst", "x")}
+    init = {k: rng.standard_normal(n) for k in f}
+
+    def run(stream):
+        cuda_lib.dll.hb_set_tuning(b"stream", stream)
+        out = {}
+        for k in f:
+            f[k].upload(init[k], L)
+        A.apply(f["src"], f["dst"], L, All)
+        out["replace"] = f["dst"].download(L)
+        A.apply(f["src"], f["dst"], L, Inner, Add)
+        out["add"] = f["dst"].download(L)
+        A.residual(f["src"], f["rhs"], f["dst"], L, Inner)
+        out["residual"] = f["dst"].download(L)
+        A.smooth_jac(f["dst"], f["rhs"], f["src"], 0.66, L, All)
+        out["jacobi"] = f["dst"].download(L)
+        A.cheb_first(f["src"], f["rhs"], f["dst"], L, All)
+        out["cheb_first"] = f["dst"].download(L)
+        A.cheb_step(f["src"], f["dst"], f["x"], 0.37, L, All)
+        out["cheb_step"] = f["dst"].download(L)
+        out["cheb_step_x"] = f["x"].download(L)
+        return out
+
+    try:
+        a, b = run(1), run(0)
+    finally:
+        cuda_lib.dll.hb_set_tuning(b"stream", 1)
+    for k in a:
+        assert np.array_equal(a[k], b[k]), (k, np.abs(a[k] - b[k]).max())
