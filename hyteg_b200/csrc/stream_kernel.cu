@@ -22,13 +22,21 @@
 
 namespace {
 
-constexpr int ZB       = 8;  // output slices per item
-constexpr int XT       = 64; // output columns per item
-constexpr int ROWLEN   = 68; // staged doubles per row segment (XT + 2 halo + 2 alignment slack)
-constexpr int ROWBYTES = ROWLEN * 8;
-constexpr int NSRC     = ZB + 2;
-constexpr int NCONS    = 8; // consumer warps
-constexpr int THREADS  = ( NCONS + 1 ) * 32;
+constexpr int NCONS   = 8;   // consumer warps = 2 warpgroups
+constexpr int THREADS = 384; // + 1 warpgroup: producer warp and three idle warps that hand their registers back
+constexpr int REGS_CONSUMER = 104; // 8 x 104 + 4 x 24 <= 12 x 80: setmaxnreg moves registers inside ONE CTA only
+constexpr int REGS_PRODUCER = 24;
+
+// geometry of a work item for XW warps along x: ZB output slices x XT output columns
+template < int XW >
+struct Geo
+{
+   static constexpr int ZB       = 2 * ( NCONS / XW );
+   static constexpr int XT       = 32 * XW;
+   static constexpr int ROWLEN   = XT + 4; // staged doubles per row segment (2 halo + 2 alignment slack)
+   static constexpr int ROWBYTES = ROWLEN * 8;
+   static constexpr int NSRC     = ZB + 2;
+};
 
 __device__ __forceinline__ uint32_t smem_u32( const void* p )
 {
@@ -122,24 +130,26 @@ __device__ __forceinline__ void hb_epilogue_stream( const HbStencilArgs& a, size
    }
 }
 
-template < int MODE, int R, int STAGES >
+template < int MODE, int XW, int R, int STAGES >
 struct Smem
 {
-   static constexpr int NR         = NSRC + ZB * ModeTraits< MODE >::nExtra; // staged row segments per input row
-   static constexpr int stageBytes = R * NR * ROWBYTES;
+   using G                         = Geo< XW >;
+   static constexpr int NR         = G::NSRC + G::ZB * ModeTraits< MODE >::nExtra; // staged row segments per input row
+   static constexpr int stageBytes = R * NR * G::ROWBYTES;
    static constexpr int dataOff    = 1024;
    static constexpr int total      = dataOff + STAGES * stageBytes;
 };
 
-template < int MODE, int R, int STAGES >
-__global__ void __maxnreg__( 112 ) hb_stream_kernel( const HbLevelView lv, const HbStencilArgs a, const HbStreamArgs sa )
+template < int MODE, int XW, int R, int STAGES >
+__global__ void __launch_bounds__( THREADS, 2 ) hb_stream_kernel( const HbLevelView lv, const HbStencilArgs a, const HbStreamArgs sa )
 {
-   using SM = Smem< MODE, R, STAGES >;
-   constexpr int NR = SM::NR;
+   using SM = Smem< MODE, XW, R, STAGES >;
+   using G  = Geo< XW >;
+   constexpr int NR = SM::NR, ROWLEN = G::ROWLEN, NSRC = G::NSRC;
    extern __shared__ __align__( 128 ) unsigned char smemRaw[];
-   StageHeader* hdr   = reinterpret_cast< StageHeader* >( smemRaw );                // STAGES * 32 B
-   uint64_t*    full  = reinterpret_cast< uint64_t* >( smemRaw + 512 );             // STAGES * 8 B
-   uint64_t*    empty = reinterpret_cast< uint64_t* >( smemRaw + 768 );             // STAGES * 8 B
+   StageHeader* hdr   = reinterpret_cast< StageHeader* >( smemRaw );    // STAGES * 32 B
+   uint64_t*    full  = reinterpret_cast< uint64_t* >( smemRaw + 512 ); // STAGES * 8 B
+   uint64_t*    empty = reinterpret_cast< uint64_t* >( smemRaw + 768 ); // STAGES * 8 B
    double*      data  = reinterpret_cast< double* >( smemRaw + SM::dataOff );
 
    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -148,7 +158,7 @@ __global__ void __maxnreg__( 112 ) hb_stream_kernel( const HbLevelView lv, const
    {
       for ( int s = 0; s < STAGES; s++ )
       {
-         mbar_init( &full[s], 1 );
+         mbar_init( &full[s], 4 ); // one arrival (with its byte count) per producer warp
          mbar_init( &empty[s], NCONS );
       }
       asm volatile( "fence.mbarrier_init.release.cluster;" ::: "memory" );
@@ -158,19 +168,27 @@ __global__ void __maxnreg__( 112 ) hb_stream_kernel( const HbLevelView lv, const
    int      stage = 0;
    uint32_t phase = 0;
 
-   if ( warp == NCONS )
+   if ( warp >= NCONS )
    {
-      // ------------------------------------------------------------------ producer warp
-      const long long arenaLimit = (long long) lv.nCells * lv.cellSize + HB_ARENA_PAD - ROWLEN - 2;
-      const double*   srcArena   = sa.srcArena;
-      const double*   extraArena = sa.extraArena;
-      const int       total      = lv.nCells * sa.nItems;
+      // ---------------------------------------------------- producer warpgroup: gives its registers to the consumers
+      asm volatile( "setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"( REGS_PRODUCER ) );
+      // Four producer warps share the copies of a stage (one row segment per lane): a single warp issuing all of them is
+      // latency-bound (ncu r1_c: consumers starved, 65 % of the samples in the full-barrier wait).
+      static_assert( R * NR <= 128, "one copy per producer lane" );
+      const int  pw    = warp - NCONS;
+      const int  k     = pw + 4 * lane; // copy handled by this lane: interleaved so that every warp gets a quarter
+      const int  j     = k / NR, q = k - j * NR;
+      const bool isSrc = q < NSRC;
+      const int  total = lv.nCells * sa.nItems;
+      int*       itemSlot = reinterpret_cast< int* >( smemRaw + 1000 );
+      const double* base  = isSrc ? sa.srcArena : sa.extraArena;
       while ( true )
       {
-         int item = 0;
-         if ( lane == 0 )
-            item = atomicAdd( sa.counter, 1 );
-         item = __shfl_sync( 0xffffffffu, item, 0 );
+         if ( threadIdx.x == NCONS * 32 )
+            *itemSlot = atomicAdd( sa.counter, 1 );
+         asm volatile( "bar.sync 1, 128;" ::: "memory" );
+         const int item = *itemSlot;
+         asm volatile( "bar.sync 2, 128;" ::: "memory" ); // slot may be overwritten after everybody has read it
          if ( item >= total )
             break;
          const int cell = item / sa.nItems;
@@ -179,43 +197,49 @@ __global__ void __maxnreg__( 112 ) hb_stream_kernel( const HbLevelView lv, const
          const HbItem    it       = sa.items[item - cell * sa.nItems];
          const int       nChunks  = ( it.nOut + 2 + R - 1 ) / R;
          const long long cellBase = (long long) cell * lv.cellSize;
+         // this lane's row segment: slice s, columns xa..xb, rows yFirst + c*R
+         const int s      = isSrc ? it.z0 - 1 + q : it.z0 + ( q - NSRC );
+         const int xa     = isSrc ? it.x0 - 1 : it.x0;
+         const int xbWant = isSrc ? it.x0 + G::XT : it.x0 + G::XT - 1;
+         const int yFirst = ( isSrc ? it.ya - 1 : it.ya - 2 ) + j;
          for ( int c = 0; c < nChunks; c++ )
          {
             mbar_wait( &empty[stage], phase ^ 1u );
-            const int yIn = it.ya - 1 + c * R;
+            double*   sdata = data + (size_t) stage * ( SM::stageBytes / 8 );
+            const int y     = yFirst + c * R;
+            const int last  = N - s - y; // last column of the row
+            const int xb    = xbWant < last ? xbWant : last;
+            long long g0    = 0;
+            int       bytes = 0;
+            if ( k < R * NR && y >= 0 && s <= N && xb >= xa )
+            {
+               const long long g  = cellBase + row_base( N, y, s ) + xa;
+               const long long g1 = ( g + ( xb - xa ) + 2 ) & ~1LL; // one past the last element, rounded up to even
+               g0                 = g & ~1LL;
+               bytes              = (int) ( g1 - g0 ) * 8;
+            }
+            int sum = bytes;
+#pragma unroll
+            for ( int o = 16; o > 0; o >>= 1 )
+               sum += __shfl_xor_sync( 0xffffffffu, sum, o );
             if ( lane == 0 )
             {
-               StageHeader h;
-               h.cell     = cell;
-               h.z0       = it.z0;
-               h.x0       = it.x0;
-               h.yIn      = yIn;
-               h.yOut0    = it.ya;
-               h.yOut1    = it.ya + it.nOut - 1;
-               hdr[stage] = h;
-               mbar_arrive_expect_tx( &full[stage], (uint32_t) SM::stageBytes );
+               if ( pw == 0 )
+               {
+                  StageHeader h;
+                  h.cell     = cell;
+                  h.z0       = it.z0;
+                  h.x0       = it.x0;
+                  h.yIn      = it.ya - 1 + c * R;
+                  h.yOut0    = it.ya;
+                  h.yOut1    = it.ya + it.nOut - 1;
+                  hdr[stage] = h;
+               }
+               mbar_arrive_expect_tx( &full[stage], (uint32_t) sum );
             }
             __syncwarp();
-            double* sdata = data + (size_t) stage * ( SM::stageBytes / 8 );
-            for ( int k = lane; k < R * NR; k += 32 )
-            {
-               const int     j = k / NR, q = k - j * NR;
-               long long     g;
-               const double* base;
-               if ( q < NSRC )
-               {
-                  g    = cellBase + row_base( N, yIn + j, it.z0 - 1 + q ) + it.x0 - 1;
-                  base = srcArena;
-               }
-               else
-               {
-                  g    = cellBase + row_base( N, yIn + j - 1, it.z0 + ( q - NSRC ) ) + it.x0;
-                  base = extraArena;
-               }
-               g = g < 0 ? 0 : ( g > arenaLimit ? arenaLimit : g );
-               g &= ~1LL;
-               tma_load_1d( sdata + k * ROWLEN, base + g, ROWBYTES, &full[stage] );
-            }
+            if ( bytes > 0 )
+               tma_load_1d( sdata + k * ROWLEN, base + g0, (uint32_t) bytes, &full[stage] );
             if ( ++stage == STAGES )
             {
                stage = 0;
@@ -223,12 +247,16 @@ __global__ void __maxnreg__( 112 ) hb_stream_kernel( const HbLevelView lv, const
             }
          }
       }
-      mbar_wait( &empty[stage], phase ^ 1u );
+      if ( pw == 0 )
+      {
+         mbar_wait( &empty[stage], phase ^ 1u );
+         if ( lane == 0 )
+            hdr[stage].cell = -1;
+      }
       if ( lane == 0 )
       {
-         hdr[stage].cell = -1;
          mbar_arrive( &full[stage] );
-         if ( atomicAdd( sa.counter + 1, 1 ) == (int) gridDim.x - 1 )
+         if ( pw == 0 && atomicAdd( sa.counter + 1, 1 ) == (int) gridDim.x - 1 )
          {
             // last CTA to run out of work re-arms the counters for the next launch
             sa.counter[0] = 0;
@@ -239,8 +267,9 @@ __global__ void __maxnreg__( 112 ) hb_stream_kernel( const HbLevelView lv, const
    }
 
    // --------------------------------------------------------------------- consumer warps
-   const int p  = warp >> 1;                  // slice pair
-   const int xl = ( ( warp & 1 ) << 5 ) + lane; // local column 0..63
+   asm volatile( "setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"( REGS_CONSUMER ) );
+   const int p  = warp / XW;                          // slice pair
+   const int xl = ( ( warp % XW ) << 5 ) + lane;      // local column
    int       curCell = -1;
    double    w[HB_NDIR];
    double    invd = 0.0;
@@ -278,7 +307,7 @@ __global__ void __maxnreg__( 112 ) hb_stream_kernel( const HbLevelView lv, const
          gi[q] = row_base( N, h.yIn, zA - 1 + q ) + h.x0 - 1 + cpar;
       }
       // output row bases (row yIn-1 of slices zA, zA+1)
-      int ob0 = row_base( N, h.yIn - 1, zA ), ob1 = row_base( N, h.yIn - 1, zA + 1 );
+      int           ob0 = row_base( N, h.yIn - 1, zA ), ob1 = row_base( N, h.yIn - 1, zA + 1 );
       const double* sdata = data + (size_t) stage * ( SM::stageBytes / 8 );
 
 #pragma unroll
@@ -338,15 +367,9 @@ __global__ void __maxnreg__( 112 ) hb_stream_kernel( const HbLevelView lv, const
             e1               = er[ROWLEN + ( ( ob1 + h.x0 + cpar ) & 1 )];
          }
          if ( ok0 )
-         {
-            const size_t gidx = (size_t) ( cellBase + ob0 + x );
-            hb_epilogue_stream< MODE >( a, gidx, s0, w[D_C], invd, q1Bc, e0 );
-         }
+            hb_epilogue_stream< MODE >( a, (size_t) ( cellBase + ob0 + x ), s0, w[D_C], invd, q1Bc, e0 );
          if ( ok1 )
-         {
-            const size_t gidx = (size_t) ( cellBase + ob1 + x );
-            hb_epilogue_stream< MODE >( a, gidx, s1, w[D_C], invd, q2Bc, e1 );
-         }
+            hb_epilogue_stream< MODE >( a, (size_t) ( cellBase + ob1 + x ), s1, w[D_C], invd, q2Bc, e1 );
 
          // slide the register window
          q0Bc = n0c;
@@ -363,9 +386,9 @@ __global__ void __maxnreg__( 112 ) hb_stream_kernel( const HbLevelView lv, const
          q2Br = n2r;
          q3Ac = q3Bc;
          q3Ar = q3Br;
-         q3Br = n3r;
          q3Bl = n3l;
          q3Bc = n3c;
+         q3Br = n3r;
 #pragma unroll
          for ( int q = 0; q < 4; q++ )
             gi[q] += ws[q] - yr;
@@ -391,6 +414,8 @@ __global__ void __maxnreg__( 112 ) hb_stream_kernel( const HbLevelView lv, const
 #include <stdexcept>
 #include <string>
 
+#define HB_STREAM_XW 1 // warps along x per item: 1 -> items of 16 slices x 32 columns, 2 -> 8 slices x 64 columns
+
 namespace {
 
 int smCount()
@@ -407,15 +432,17 @@ int smCount()
    return n;
 }
 
-template < int MODE, int R, int STAGES >
+template < int MODE, int XW, int R, int STAGES >
 void launchMode( const HbLevelView& lv, const HbStencilArgs& a, const HbStreamArgs& sa, cudaStream_t st )
 {
-   using SM           = Smem< MODE, R, STAGES >;
+   using SM           = Smem< MODE, XW, R, STAGES >;
    static bool once   = false;
-   auto        kernel = hb_stream_kernel< MODE, R, STAGES >;
+   auto        kernel = hb_stream_kernel< MODE, XW, R, STAGES >;
    if ( !once )
    {
       cudaError_t e = cudaFuncSetAttribute( kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SM::total );
+      if ( e == cudaSuccess )
+         e = cudaFuncSetAttribute( kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared );
       if ( e != cudaSuccess )
          throw std::runtime_error( std::string( "hyteg_b200: cudaFuncSetAttribute: " ) + cudaGetErrorString( e ) );
       once = true;
@@ -441,45 +468,35 @@ bool hb_stream_supported( int mode, const HbLevelView& lv )
 
 void hb_launch_stream_stencil( int mode, const HbLevelView& lv, const HbStencilArgs& a, const HbStreamArgs& sa, cudaStream_t st )
 {
+   constexpr int XW = HB_STREAM_XW;
    switch ( mode )
    {
    case HB_APPLY_REPLACE:
-      launchMode< HB_APPLY_REPLACE, 4, 5 >( lv, a, sa, st );
+      launchMode< HB_APPLY_REPLACE, XW, 2, 6 >( lv, a, sa, st );
       break;
    case HB_APPLY_ADD:
-      launchMode< HB_APPLY_ADD, 2, 5 >( lv, a, sa, st );
+      launchMode< HB_APPLY_ADD, XW, 2, 4 >( lv, a, sa, st );
       break;
    case HB_RESIDUAL:
-      launchMode< HB_RESIDUAL, 2, 5 >( lv, a, sa, st );
+      launchMode< HB_RESIDUAL, XW, 2, 4 >( lv, a, sa, st );
       break;
    case HB_JACOBI:
-      launchMode< HB_JACOBI, 2, 5 >( lv, a, sa, st );
+      launchMode< HB_JACOBI, XW, 2, 4 >( lv, a, sa, st );
       break;
    case HB_CHEB_FIRST:
-      launchMode< HB_CHEB_FIRST, 2, 5 >( lv, a, sa, st );
+      launchMode< HB_CHEB_FIRST, XW, 2, 4 >( lv, a, sa, st );
       break;
    case HB_CHEB_STEP:
-      launchMode< HB_CHEB_STEP, 2, 5 >( lv, a, sa, st );
+      launchMode< HB_CHEB_STEP, XW, 2, 4 >( lv, a, sa, st );
       break;
    default:
       throw std::runtime_error( "hyteg_b200: mode not supported by the streamed kernel" );
    }
 }
 
-#else // HB_EMUL: the streamed kernel needs TMA + mbarriers; the emulation build always uses the generic kernel
-
-bool hb_stream_supported( int, const HbLevelView& )
-{
-   return false;
-}
-void hb_launch_stream_stencil( int, const HbLevelView&, const HbStencilArgs&, const HbStreamArgs&, cudaStream_t ) {}
-
-#endif
-
-// Items of one macro-cell: z blocks of 8 slices x column blocks of 64 x row segments of <= 30 rows.
 void hb_stream_build_items( int N, std::vector< HbItem >& items )
 {
-   const int ZBh = 8, XTh = 64, YS = 30;
+   const int ZBh = 2 * ( 8 / HB_STREAM_XW ), XTh = 32 * HB_STREAM_XW, YS = 30;
    items.clear();
    for ( int z0 = 1; z0 <= N - 3; z0 += ZBh )
       for ( int x0 = 1; x0 <= N - 2 - z0; x0 += XTh )
@@ -496,3 +513,17 @@ void hb_stream_build_items( int N, std::vector< HbItem >& items )
          }
       }
 }
+
+#else // HB_EMUL: the streamed kernel needs TMA + mbarriers; the emulation build always uses the generic kernel
+
+bool hb_stream_supported( int, const HbLevelView& )
+{
+   return false;
+}
+void hb_launch_stream_stencil( int, const HbLevelView&, const HbStencilArgs&, const HbStreamArgs&, cudaStream_t ) {}
+void hb_stream_build_items( int, std::vector< HbItem >& items )
+{
+   items.clear();
+}
+
+#endif
