@@ -129,6 +129,8 @@ hb::LevelTables& hb_storage::level( int L )
       std::vector< HbItem > items;
       hb_stream_build_items( N, items );
       lt->items.upload( items );
+      hb_shuffle_build_items( N, items );
+      lt->itemsShuffle.upload( items );
    }
    lt->scratch.alloc( (size_t) view.nLocal * bnd.size() );
    HbLevelView& v = lt->view;

@@ -10,6 +10,7 @@
 #include "hb_device.h"
 #include "kernels.h"
 #include "stream_kernel.h"
+#include "shuffle_kernel.h"
 #include "topology.hpp"
 
 namespace hb {
@@ -54,7 +55,8 @@ struct LevelTables
    DeviceBuffer< HbBndPoint > bnd, xyz;
    DeviceBuffer< uint8_t >    mask;
    DeviceBuffer< HbTile >     tiles;
-   DeviceBuffer< HbItem >     items;   // work items of the streamed interior kernel
+   DeviceBuffer< HbItem >     items;   // work items of the TMA-streamed interior kernel
+   DeviceBuffer< HbItem >     itemsShuffle; // work items of the centre-column + shuffle interior kernel
    DeviceBuffer< double >     scratch; // nCells*nBnd, interface staging (SOR)
    std::vector< HbBndPoint >  hXyz;    // host copy of the coordinate template
 };

@@ -1,0 +1,11 @@
+// Launcher of the centre-column + shuffle interior stencil kernel (shuffle_kernel.cu).
+#pragma once
+#include <vector>
+
+#include "stream_kernel.h" // HbItem, HbStreamArgs, HB_ARENA_PAD
+
+bool hb_shuffle_supported( int mode, const HbLevelView& lv );
+// work items of one macro-cell for N subdivisions: 16 slices x 30 columns x <= 45 rows
+void hb_shuffle_build_items( int N, std::vector< HbItem >& items );
+// interior points only; the interface points are handled by hb_launch_stencil( ..., interior=false, boundary=true )
+void hb_launch_shuffle_stencil( int mode, const HbLevelView& lv, const HbStencilArgs& a, const HbStreamArgs& sa, cudaStream_t st );

@@ -278,6 +278,8 @@ __global__ void __launch_bounds__( THREADS, 2 ) hb_stream_kernel( const HbLevelV
    double q1Ac = 0, q1Ar = 0, q1Bl = 0, q1Bc = 0, q1Br = 0;
    double q2Ac = 0, q2Ar = 0, q2Bl = 0, q2Bc = 0, q2Br = 0;
    double q3Ac = 0, q3Ar = 0, q3Bl = 0, q3Bc = 0, q3Br = 0;
+   long long cellBase = 0;
+   int       zA = 0, x = 0, cpar = 0, gi[4] = { 0, 0, 0, 0 }, ob0 = 0, ob1 = 0, yMax0 = -1, yMax1 = -1, yMin = 0;
 
    while ( true )
    {
@@ -285,29 +287,32 @@ __global__ void __launch_bounds__( THREADS, 2 ) hb_stream_kernel( const HbLevelV
       const StageHeader h = hdr[stage];
       if ( h.cell < 0 )
          break;
-      if ( h.cell != curCell )
+      if ( h.yIn == h.yOut0 - 1 )
       {
-         curCell                       = h.cell;
-         const double* __restrict__ Wc = a.W + (size_t) h.cell * HB_NMASK * HB_NDIR;
+         // first chunk of a work item: (re)load the weights and derive the per-thread index state once per item
+         if ( h.cell != curCell )
+         {
+            curCell                       = h.cell;
+            const double* __restrict__ Wc = a.W + (size_t) h.cell * HB_NMASK * HB_NDIR;
 #pragma unroll
-         for ( int d = 0; d < HB_NDIR; d++ )
-            w[d] = __ldg( Wc + d );
-         invd = 1.0 / w[D_C];
-      }
-      const long long cellBase = (long long) h.cell * lv.cellSize;
-      const int       zA       = h.z0 + 2 * p;
-      const int       x        = h.x0 + xl;
-      // parity of the staged row segments (global element index of their first element)
-      const int cpar = (int) ( cellBase & 1 );
-      int       gi[4], ws[4];
+            for ( int d = 0; d < HB_NDIR; d++ )
+               w[d] = __ldg( Wc + d );
+            invd = 1.0 / w[D_C];
+         }
+         cellBase = (long long) h.cell * lv.cellSize;
+         zA       = h.z0 + 2 * p;
+         x        = h.x0 + xl;
+         cpar     = (int) ( cellBase & 1 );
 #pragma unroll
-      for ( int q = 0; q < 4; q++ )
-      {
-         ws[q] = N + 1 - ( zA - 1 + q );
-         gi[q] = row_base( N, h.yIn, zA - 1 + q ) + h.x0 - 1 + cpar;
+         for ( int q = 0; q < 4; q++ )
+            gi[q] = row_base( N, h.yIn, zA - 1 + q ) + h.x0 - 1 + cpar; // parity of the staged row segments
+         ob0 = row_base( N, h.yIn - 1, zA ); // output row bases (row yIn-1 of slices zA, zA+1)
+         ob1 = row_base( N, h.yIn - 1, zA + 1 );
+         // last valid output row of this thread's column in its two slices (-1: none)
+         yMax0 = ( zA <= N - 3 ) ? min( h.yOut1, min( N - 2 - zA, N - 1 - zA - x ) ) : -1;
+         yMax1 = ( zA + 1 <= N - 3 ) ? min( h.yOut1, min( N - 3 - zA, N - 2 - zA - x ) ) : -1;
+         yMin  = h.yOut0;
       }
-      // output row bases (row yIn-1 of slices zA, zA+1)
-      int           ob0 = row_base( N, h.yIn - 1, zA ), ob1 = row_base( N, h.yIn - 1, zA + 1 );
       const double* sdata = data + (size_t) stage * ( SM::stageBytes / 8 );
 
 #pragma unroll
@@ -356,9 +361,8 @@ __global__ void __launch_bounds__( THREADS, 2 ) hb_stream_kernel( const HbLevelV
          s1 += w[D_TS] * q3Ac;
          s1 += w[D_TSE] * q3Ar;
 
-         const bool rowOk = ( yo >= h.yOut0 ) && ( yo <= h.yOut1 );
-         const bool ok0   = rowOk && ( zA <= N - 3 ) && ( yo <= N - 2 - zA ) && ( x <= N - 1 - yo - zA );
-         const bool ok1   = rowOk && ( zA + 1 <= N - 3 ) && ( yo <= N - 3 - zA ) && ( x <= N - 2 - yo - zA );
+         const bool ok0 = ( yo >= yMin ) && ( yo <= yMax0 );
+         const bool ok1 = ( yo >= yMin ) && ( yo <= yMax1 );
          double     e0 = 0.0, e1 = 0.0;
          if ( ModeTraits< MODE >::nExtra )
          {
@@ -391,7 +395,7 @@ __global__ void __launch_bounds__( THREADS, 2 ) hb_stream_kernel( const HbLevelV
          q3Br = n3r;
 #pragma unroll
          for ( int q = 0; q < 4; q++ )
-            gi[q] += ws[q] - yr;
+            gi[q] += ( N + 2 - zA - q ) - yr; // next row of slice zA-1+q
          ob0 += ( N + 1 - zA ) - yo;
          ob1 += ( N - zA ) - yo;
       }
@@ -414,7 +418,7 @@ __global__ void __launch_bounds__( THREADS, 2 ) hb_stream_kernel( const HbLevelV
 #include <stdexcept>
 #include <string>
 
-#define HB_STREAM_XW 1 // warps along x per item: 1 -> items of 16 slices x 32 columns, 2 -> 8 slices x 64 columns
+#define HB_STREAM_XW 2 // warps along x per item: 1 -> items of 16 slices x 32 columns, 2 -> 8 slices x 64 columns
 
 namespace {
 

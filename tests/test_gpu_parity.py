@@ -109,7 +109,7 @@ def test_full_size_properties(cuda_lib):
 
 
 @pytest.mark.parametrize("name,L", [("cube_6el", 5), ("cube_6el", 6), ("regular_octahedron_8el", 5), ("tet_tilted_1el", 7)])
-def test_streamed_kernel_bit_identical_to_generic(cuda_lib, name, L):
+def test_interior_kernels_agree(cuda_lib, name, L):
     """the TMA-streamed interior kernel uses the same operation order as the generic kernel: results must be bitwise equal
     for every fused mode (apply replace/add, residual, Jacobi, Chebyshev first/step)"""
     v, c = meshes.golden(name)
@@ -122,7 +122,7 @@ def test_streamed_kernel_bit_identical_to_generic(cuda_lib, name, L):
     init = {k: rng.standard_normal(n) for k in f}
 
     def run(stream):
-        cuda_lib.dll.hb_set_tuning(b"stream", stream)
+        cuda_lib.dll.hb_set_tuning(b"interior", stream)
         out = {}
         for k in f:
             f[k].upload(init[k], L)
@@ -142,8 +142,11 @@ def test_streamed_kernel_bit_identical_to_generic(cuda_lib, name, L):
         return out
 
     try:
-        a, b = run(1), run(0)
+        a, b, c = run(2), run(0), run(1)
     finally:
-        cuda_lib.dll.hb_set_tuning(b"stream", 1)
+        cuda_lib.dll.hb_set_tuning(b"interior", 2)
     for k in a:
-        assert np.array_equal(a[k], b[k]), (k, np.abs(a[k] - b[k]).max())
+        # TMA-streamed kernel: same operation order as the generic kernel -> bitwise equal
+        assert np.array_equal(c[k], b[k]), (k, np.abs(c[k] - b[k]).max())
+        # shuffle kernel: the 15 taps are summed in three column groups -> equal up to rounding
+        assert np.abs(a[k] - b[k]).max() <= 1e-13 * np.abs(b[k]).max(), (k, np.abs(a[k] - b[k]).max())
