@@ -40,6 +40,8 @@ int tuning( const std::string& key, int dflt )
 
 using namespace hb;
 
+static const hb_operator* g_constOwner = nullptr; // operator whose interior weights + cell flags sit in constant memory
+
 #define HB_TRY try {
 #define HB_CATCH( ret )                   \
    }                                      \
@@ -77,6 +79,7 @@ void hb_storage::uploadTopologyTables()
       kv.second->view.nSlots = (int) view.slotGlobal.size();
    }
    tablesDirty = false;
+   g_constOwner = nullptr; // macro-cell flags may have changed
 }
 
 hb::LevelTables& hb_storage::level( int L )

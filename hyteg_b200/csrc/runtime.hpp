@@ -100,4 +100,8 @@ struct hb_operator
    std::vector< hb::DeviceBuffer< double > > W;  // per level [nSlots][16][15]
    std::vector< std::vector< double > >      hW; // host copy
    const double* weights( int L ) const;
+   // interior weights of all levels in constant memory (shuffle kernel): entry of (level L, local cell c) = constBase(L) + c
+   bool constUsable() const;
+   int  constBase( int L ) const;
+   void ensureConstWeights();
 };

@@ -26,7 +26,13 @@ namespace {
 
 constexpr int PAIRS = 8;  // warps per CTA = z-slice pairs per work item -> 16 output slices
 constexpr int XOUT  = 30; // output columns per warp
-constexpr int DEPTH = 3;  // rows in flight ahead of the row being computed
+constexpr int DEPTH_DEFAULT = 5; // rows in flight ahead of the row being computed (template parameter DEPTH)
+
+// Interior stencil weights of (level, macro-cell) pairs.  Read with a CTA-uniform index, so they live in UNIFORM registers
+// (LDCU.64 UR, c[0x3][UR+imm]) and enter the DFMAs as uniform operands: no vector registers are spent on the 15 weights,
+// which is what makes room for the DEPTH-row prefetch ring at 2 x 8 warps per SM.
+__constant__ double  c_W[HB_CONST_W_ENTRIES][16];
+__constant__ uint8_t c_bflag[HB_CONST_W_ENTRIES]; // meshBoundaryFlag of the macro-cell of each entry
 
 __device__ __forceinline__ int tet( int k )
 {
@@ -69,15 +75,17 @@ __device__ __forceinline__ void epilogue( const HbStencilArgs& a, size_t gi, dou
 
 namespace {
 
-template < int MODE >
+template < int MODE, int DEPTH >
 __global__ void __launch_bounds__( PAIRS * 32, 2 ) hb_shuffle_kernel( const HbLevelView lv, const HbStencilArgs a, const HbStreamArgs sa )
 {
    constexpr bool EX = ModeTraits< MODE >::hasExtra;
    const int      N  = lv.N;
-   const int      cell = blockIdx.x / sa.nItems;
-   if ( !( ( sa.selMask >> lv.cells[cell].region[0].bflag ) & 1 ) )
+   // item-major order, items sorted by decreasing work: the last wave of CTAs consists of the smallest items
+   const int itemIdx = blockIdx.x / lv.nCells;
+   const int cell    = blockIdx.x - itemIdx * lv.nCells;
+   if ( !( ( sa.selMask >> c_bflag[sa.constBase + cell] ) & 1 ) )
       return;
-   const HbItem it   = sa.items[blockIdx.x - cell * sa.nItems];
+   const HbItem it   = sa.items[itemIdx];
    const int    warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
    const int    zA   = it.z0 + 2 * warp; // this warp's output slices zA, zA+1
    if ( zA > N - 3 )
@@ -87,14 +95,8 @@ __global__ void __launch_bounds__( PAIRS * 32, 2 ) hb_shuffle_kernel( const HbLe
    const double* __restrict__ S = sa.srcArena + cellBase;
    const double* __restrict__ E = EX ? sa.extraArena + cellBase : nullptr;
 
-   double w[HB_NDIR];
-   {
-      const double* __restrict__ Wc = a.W + (size_t) cell * HB_NMASK * HB_NDIR;
-#pragma unroll
-      for ( int d = 0; d < HB_NDIR; d++ )
-         w[d] = __ldg( Wc + d );
-   }
-   const double invd = 1.0 / w[D_C];
+   const double* w    = c_W[sa.constBase + cell];
+   const double  invd = w[15]; // 1 / w[D_C], stored behind the 15 weights
 
    const int yFirstIn = it.ya - 1;       // first input row
    const int yLastIn  = it.ya + it.nOut; // last input row
@@ -210,51 +212,86 @@ __global__ void __launch_bounds__( PAIRS * 32, 2 ) hb_shuffle_kernel( const HbLe
 // ---------------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------------
+#include <algorithm>
 #include <stdexcept>
+#include <string>
+
+void hb_shuffle_upload_weights( int first, int n, const double* w16, const uint8_t* bflag, cudaStream_t st )
+{
+   if ( first < 0 || n < 0 || first + n > HB_CONST_W_ENTRIES )
+      throw std::runtime_error( "hyteg_b200: constant-memory weight table overflow" );
+   if ( n == 0 )
+      return;
+   cudaError_t e = cudaMemcpyToSymbolAsync( c_W, w16, (size_t) n * 16 * sizeof( double ), (size_t) first * 16 * sizeof( double ), cudaMemcpyHostToDevice, st );
+   if ( e == cudaSuccess )
+      e = cudaMemcpyToSymbolAsync( c_bflag, bflag, (size_t) n, (size_t) first, cudaMemcpyHostToDevice, st );
+   if ( e != cudaSuccess )
+      throw std::runtime_error( std::string( "hyteg_b200: cudaMemcpyToSymbolAsync: " ) + cudaGetErrorString( e ) );
+}
 
 bool hb_shuffle_supported( int mode, const HbLevelView& lv )
 {
-   if ( lv.N < 32 || lv.nCells == 0 )
+   if ( lv.N < 32 || lv.nCells == 0 || lv.nCells > HB_CONST_W_ENTRIES )
       return false;
    return mode == HB_APPLY_REPLACE || mode == HB_APPLY_ADD || mode == HB_RESIDUAL || mode == HB_JACOBI || mode == HB_CHEB_FIRST ||
           mode == HB_CHEB_STEP;
 }
 
-void hb_launch_shuffle_stencil( int mode, const HbLevelView& lv, const HbStencilArgs& a, const HbStreamArgs& sa, cudaStream_t st )
+template < int DEPTH >
+static void launchDepth( int mode, unsigned g, unsigned b, const HbLevelView& lv, const HbStencilArgs& a, const HbStreamArgs& sa, cudaStream_t st )
 {
-   const long long grid = (long long) lv.nCells * sa.nItems;
-   if ( grid < 1 )
-      return;
-   const unsigned g = (unsigned) grid, b = PAIRS * 32;
    switch ( mode )
    {
    case HB_APPLY_REPLACE:
-      hb_shuffle_kernel< HB_APPLY_REPLACE ><<< g, b, 0, st >>>( lv, a, sa );
+      hb_shuffle_kernel< HB_APPLY_REPLACE, DEPTH ><<< g, b, 0, st >>>( lv, a, sa );
       break;
    case HB_APPLY_ADD:
-      hb_shuffle_kernel< HB_APPLY_ADD ><<< g, b, 0, st >>>( lv, a, sa );
+      hb_shuffle_kernel< HB_APPLY_ADD, DEPTH ><<< g, b, 0, st >>>( lv, a, sa );
       break;
    case HB_RESIDUAL:
-      hb_shuffle_kernel< HB_RESIDUAL ><<< g, b, 0, st >>>( lv, a, sa );
+      hb_shuffle_kernel< HB_RESIDUAL, DEPTH ><<< g, b, 0, st >>>( lv, a, sa );
       break;
    case HB_JACOBI:
-      hb_shuffle_kernel< HB_JACOBI ><<< g, b, 0, st >>>( lv, a, sa );
+      hb_shuffle_kernel< HB_JACOBI, DEPTH ><<< g, b, 0, st >>>( lv, a, sa );
       break;
    case HB_CHEB_FIRST:
-      hb_shuffle_kernel< HB_CHEB_FIRST ><<< g, b, 0, st >>>( lv, a, sa );
+      hb_shuffle_kernel< HB_CHEB_FIRST, DEPTH ><<< g, b, 0, st >>>( lv, a, sa );
       break;
    case HB_CHEB_STEP:
-      hb_shuffle_kernel< HB_CHEB_STEP ><<< g, b, 0, st >>>( lv, a, sa );
+      hb_shuffle_kernel< HB_CHEB_STEP, DEPTH ><<< g, b, 0, st >>>( lv, a, sa );
       break;
    default:
       throw std::runtime_error( "hyteg_b200: mode not supported by the shuffle kernel" );
    }
 }
 
+void hb_launch_shuffle_stencil( int mode, const HbLevelView& lv, const HbStencilArgs& a, const HbStreamArgs& sa, cudaStream_t st, int depth )
+{
+   const long long grid = (long long) lv.nCells * sa.nItems;
+   if ( grid < 1 )
+      return;
+   const unsigned g = (unsigned) grid, b = PAIRS * 32;
+   switch ( depth )
+   {
+   case 3:
+      launchDepth< 3 >( mode, g, b, lv, a, sa, st );
+      break;
+   case 7:
+      launchDepth< 7 >( mode, g, b, lv, a, sa, st );
+      break;
+   case 9:
+      launchDepth< 9 >( mode, g, b, lv, a, sa, st );
+      break;
+   default:
+      launchDepth< DEPTH_DEFAULT >( mode, g, b, lv, a, sa, st );
+   }
+}
+
 void hb_shuffle_build_items( int N, std::vector< HbItem >& items )
 {
-   const int ZBh = 2 * PAIRS, YS = 45; // 45 output rows + 2 halo rows = 47 input rows (not a multiple of DEPTH on purpose? no: any)
+   const int ZBh = 2 * PAIRS, YS = 45;
    items.clear();
+   std::vector< long long > work;
    for ( int z0 = 1; z0 <= N - 3; z0 += ZBh )
       for ( int x0 = 1; x0 <= N - 2 - z0; x0 += XOUT )
       {
@@ -269,6 +306,12 @@ void hb_shuffle_build_items( int N, std::vector< HbItem >& items )
             items.push_back( it );
          }
       }
+   // largest items first (work ~ rows x active warps): the tail of the grid is made of the small items at the diagonal
+   auto cost = [N]( const HbItem& it ) {
+      const int nz = std::min( 2 * PAIRS, N - 2 - it.z0 );
+      return (long long) ( it.nOut + 2 + DEPTH_DEFAULT ) * ( ( nz + 1 ) / 2 );
+   };
+   std::stable_sort( items.begin(), items.end(), [&]( const HbItem& a, const HbItem& b ) { return cost( a ) > cost( b ); } );
 }
 
 #else // HB_EMUL
@@ -277,10 +320,11 @@ bool hb_shuffle_supported( int, const HbLevelView& )
 {
    return false;
 }
-void hb_launch_shuffle_stencil( int, const HbLevelView&, const HbStencilArgs&, const HbStreamArgs&, cudaStream_t ) {}
+void hb_launch_shuffle_stencil( int, const HbLevelView&, const HbStencilArgs&, const HbStreamArgs&, cudaStream_t, int ) {}
 void hb_shuffle_build_items( int, std::vector< HbItem >& items )
 {
    items.clear();
 }
+void hb_shuffle_upload_weights( int, int, const double*, const uint8_t*, cudaStream_t ) {}
 
 #endif

@@ -8,4 +8,6 @@ bool hb_shuffle_supported( int mode, const HbLevelView& lv );
 // work items of one macro-cell for N subdivisions: 16 slices x 30 columns x <= 45 rows
 void hb_shuffle_build_items( int N, std::vector< HbItem >& items );
 // interior points only; the interface points are handled by hb_launch_stencil( ..., interior=false, boundary=true )
-void hb_launch_shuffle_stencil( int mode, const HbLevelView& lv, const HbStencilArgs& a, const HbStreamArgs& sa, cudaStream_t st );
+void hb_launch_shuffle_stencil( int mode, const HbLevelView& lv, const HbStencilArgs& a, const HbStreamArgs& sa, cudaStream_t st, int depth = 0 );
+// uploads n weight sets ( 15 weights + 1/w[0] each, 16 doubles ) and the macro-cells' meshBoundaryFlags to constant-memory entries [first, first+n)
+void hb_shuffle_upload_weights( int first, int n, const double* w16, const uint8_t* bflag, cudaStream_t st );

@@ -5,6 +5,7 @@
 #include "hb_device.h"
 #include "kernels.h"
 
+#define HB_CONST_W_ENTRIES 448 // (level, macro-cell) weight sets held in constant memory (56 KB)
 #define HB_ARENA_PAD 128 // doubles appended to every function arena so that staged row segments may overrun
 
 // one work item of the streamed kernel, identical for every macro-cell of a level
@@ -22,6 +23,7 @@ struct HbStreamArgs
    const HbItem* items;
    int32_t       nItems;
    uint32_t      selMask; // bit f set: macro primitives with meshBoundaryFlag f are selected by (bc, flag)
+   int32_t       constBase;                        // shuffle kernel: first entry of this level's weights in constant memory
    int32_t*      counter; // [2] work counter + finished-CTA counter, both zero between launches
 };
 

@@ -20,6 +20,10 @@ def t(fn, n=20):
     for _ in range(n): fn()
     b.record(s); torch.cuda.synchronize()
     return a.elapsed_time(b) / n * 1e3
+for depth in (3, 5, 7, 9):
+    lib.dll.hb_set_tuning(b"shuffle_depth", depth); lib.dll.hb_set_tuning(b"apply_parts", 1)
+    print("depth", depth, "interior %.1f us" % t(lambda: A.apply(src, dst, L, hb.All)))
+lib.dll.hb_set_tuning(b"shuffle_depth", 0)
 for parts in (1, 2, 3):
     lib.dll.hb_set_tuning(b"apply_parts", parts)
     print("apply_parts", parts, "%.1f us" % t(lambda: A.apply(src, dst, L, hb.All)))
