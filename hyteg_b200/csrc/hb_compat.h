@@ -79,6 +79,11 @@ inline cudaError_t cudaMemcpy( void* d, const void* s, size_t n, cudaMemcpyKind 
    std::memmove( d, s, n );
    return 0;
 }
+inline cudaError_t cudaMemset( void* d, int v, size_t n )
+{
+   std::memset( d, v, n );
+   return 0;
+}
 inline cudaError_t cudaMemsetAsync( void* d, int v, size_t n, cudaStream_t )
 {
    std::memset( d, v, n );

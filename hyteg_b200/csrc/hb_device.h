@@ -127,51 +127,69 @@ __device__ __forceinline__ void
       *out = 1.0 / diag;
 }
 
-// Stencil at a point on the boundary of macro-cell 'cell' (local index): sum of the partial
-// stencils of every macro-cell that contains the point, visited in ascending global cell id so
-// that all copies of the point produce bit-identical results.  The partial stencil of one cell is
-// exactly HyTeG's calculateStencilInMacroCellForm_new (reference P1Elements.hpp:465-515); the sum
-// over the neighbouring cells is how HyTeG builds its macro-face/edge/vertex stencils
-// (reference P1Elements.hpp:626-720, 870-1017).
+// Stencil at an interface point (x,y,z) of region 'mask' of macro-cell 'cell': sum of the partial stencils of every
+// macro-cell that contains the point, visited in ascending global cell id so that all copies of the point produce
+// bit-identical results.  The partial stencil of one cell is exactly HyTeG's calculateStencilInMacroCellForm_new
+// (reference P1Elements.hpp:465-515); the sum over the neighbouring cells is how HyTeG builds its macro-face/edge/vertex
+// stencils (reference P1Elements.hpp:626-720, 870-1017).  All threads of a block work on the same (cell, region), so the
+// region-copy entries, their weights and the valid-direction masks are block-uniform.
 __device__ __forceinline__ void hb_boundary_stencil( const HbLevelView&   lv,
                                                      const double*        W,
                                                      const double* const* src,
-                                                     int                  cell,
+                                                     const HbCellInfo*    ci,
+                                                     int                  mask,
                                                      int                  x,
                                                      int                  y,
                                                      int                  z,
                                                      double&              sNb,
                                                      double&              diag )
 {
-   const int        N  = lv.N;
-   const HbCellInfo ci = lv.cells[cell];
-   const int        b[4] = { N - x - y - z, x, y, z };
-   int              supp = 0;
-#pragma unroll
-   for ( int j = 0; j < 4; j++ )
-      supp |= ( b[j] != 0 ) << j;
-   sNb  = 0.0;
-   diag = 0.0;
-   for ( int e = ci.copyBegin; e < ci.copyEnd; e++ )
+   const int N = lv.N;
+   sNb         = 0.0;
+   diag        = 0.0;
+   const int e0 = ci->rcBegin[mask], e1 = ci->rcBegin[mask + 1];
+   for ( int e = e0; e < e1; e++ )
    {
-      const HbCopy cp = lv.copies[e];
-      if ( supp & ~cp.sharedMask )
-         continue;
-      int bp[4] = { 0, 0, 0, 0 };
-#pragma unroll
-      for ( int j = 0; j < 4; j++ )
-         if ( ( supp >> j ) & 1 )
-            bp[cp.vmap[j]] = b[j];
-      const int     xp = bp[1], yp = bp[2], zp = bp[3];
-      const int     mp = hb_mask( N, xp, yp, zp );
-      const double* w  = W + ( (size_t) cp.slot * HB_NMASK + mp ) * HB_NDIR;
-      const double* s  = src[cp.slot];
-      const int     vm = hb_valid[mp];
-      double        part = 0.0;
+      const HbRegionCopy rc = lv.regionCopies[e];
+      const int          xp = rc.c[0][0] * N + rc.c[0][1] * x + rc.c[0][2] * y + rc.c[0][3] * z;
+      const int          yp = rc.c[1][0] * N + rc.c[1][1] * x + rc.c[1][2] * y + rc.c[1][3] * z;
+      const int          zp = rc.c[2][0] * N + rc.c[2][1] * x + rc.c[2][2] * y + rc.c[2][3] * z;
+      const double* __restrict__ w = W + ( (size_t) rc.slot * HB_NMASK + rc.maskp ) * HB_NDIR;
+      const double* __restrict__ s = src[rc.slot];
+      const int                  vm = hb_valid[rc.maskp];
+      // linear index of the image point and the index deltas of the six (dy,dz) row changes of the 15-point stencil
+      const int ws   = N + 1 - zp;                // width of slice zp
+      const int i0   = hb_index( N, xp, yp, zp );
+      const int szUp = ( ws * ( ws + 1 ) ) / 2;   // size of slice zp   (distance to slice zp+1)
+      const int szDn = ( ( ws + 1 ) * ( ws + 2 ) ) / 2; // size of slice zp-1
+      const int dN = ws - yp, dS = -( ws - yp + 1 );        // (0,+1,0), (0,-1,0)
+      const int dT = szUp - yp, dTS = szUp - ws;            // (0,0,+1), (0,-1,+1)
+      const int dB = yp - szDn, dBN = ws + 1 - szDn;        // (0,0,-1), (0,+1,-1)
+      // all 14 neighbour loads are issued together; a direction that leaves the macro-cell has weight 0 in W[.][maskp]
+      // (stencil_assembly.cpp) and reads the centre instead, so the access stays inside the array
+      int idx[HB_NDIR];
+      idx[D_W]   = i0 - 1;
+      idx[D_E]   = i0 + 1;
+      idx[D_N]   = i0 + dN;
+      idx[D_S]   = i0 + dS;
+      idx[D_NW]  = i0 + dN - 1;
+      idx[D_SE]  = i0 + dS + 1;
+      idx[D_TC]  = i0 + dT;
+      idx[D_TW]  = i0 + dT - 1;
+      idx[D_TS]  = i0 + dTS;
+      idx[D_TSE] = i0 + dTS + 1;
+      idx[D_BC]  = i0 + dB;
+      idx[D_BN]  = i0 + dBN;
+      idx[D_BE]  = i0 + dB + 1;
+      idx[D_BNW] = i0 + dBN - 1;
+      double v[HB_NDIR];
 #pragma unroll
       for ( int d = 1; d < HB_NDIR; d++ )
-         if ( ( vm >> d ) & 1 )
-            part += w[d] * s[hb_index( N, xp + hb_dir[d][0], yp + hb_dir[d][1], zp + hb_dir[d][2] )];
+         v[d] = s[( ( vm >> d ) & 1 ) ? idx[d] : i0];
+      double part = 0.0;
+#pragma unroll
+      for ( int d = 1; d < HB_NDIR; d++ )
+         part += w[d] * v[d];
       sNb += part;
       diag += w[0];
    }

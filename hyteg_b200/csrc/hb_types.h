@@ -34,9 +34,26 @@ struct HbRegion
    uint8_t dim;     // 0 vertex, 1 edge, 2 face, 3 cell interior, 255 invalid mask
 };
 
+// One macro-cell contributing to the stencil of an interface region (macro face / edge / vertex) of another macro-cell:
+// a point (x,y,z) of the region has the coordinates p' = c * (N,x,y,z) in macro-cell 'slot', where it lies on region maskp.
+struct HbRegionCopy
+{
+   int32_t slot;    // index into cell pointer table / W table
+   uint8_t maskp;   // boundary mask of the image point in 'slot' (constant over the region)
+   int8_t  c[3][4]; // rows x', y', z'; columns N, x, y, z
+   uint8_t pad[3];
+};
+
+// A run of <= 256 interface points of one region in the (mask-sorted) interface point list of a level
+struct HbBndChunk
+{
+   int32_t first, count, mask, pad;
+};
+
 struct HbCellInfo
 {
    HbRegion region[HB_NMASK];
+   int32_t  rcBegin[HB_NMASK + 1]; // region copies of region m: [rcBegin[m], rcBegin[m+1]) (ascending global cell id)
    int32_t  copyBegin; // range in the copy list (sorted by global cell id, contains the cell itself)
    int32_t  copyEnd;
    int32_t  globalId;
@@ -75,12 +92,16 @@ struct HbLevelView
    int32_t nBnd;      // boundary points per macro-cell
    int32_t nTiles;    // interior tiles per macro-cell
    int32_t tileRows;  // rows marched per tile
-   const HbBndPoint* bnd;   // [nBnd]     (identical for every macro-cell)
+   const HbBndPoint* bnd;   // [nBnd]     (identical for every macro-cell), sorted by mask
    const uint8_t*    mask;  // [cellSize] boundary mask per local array index
    const HbBndPoint* xyz;   // [cellSize] logical coordinates + mask per local array index
    const HbTile*     tiles; // [nTiles]
    const HbCellInfo* cells; // [nSlots] (copy ranges only valid for the first nCells)
    const HbCopy*     copies;
+   const HbRegionCopy* regionCopies;
+   const HbBndChunk*   chunks; // [nChunks] interface points grouped by region (identical for every macro-cell)
+   int32_t             nChunks;
+   int32_t             pad0;
 };
 
 // BoundaryCondition of a function: meshBoundaryFlag -> DoFType

@@ -122,26 +122,32 @@ __device__ __forceinline__ void hb_interior_tile( const HbLevelView& lv, const H
 #undef HB_ROWBASE
 }
 
+// One block = one chunk (<= 256 points of ONE interface region) of one macro-cell.
 template < int MODE >
-__device__ __forceinline__ void hb_boundary_item( const HbLevelView& lv, const HbStencilArgs& a, long long item )
+__device__ __forceinline__ void hb_boundary_block( const HbLevelView& lv, const HbStencilArgs& a, int blk )
 {
-   const int cell = (int) ( item / lv.nBnd );
-   const int i    = (int) ( item - (long long) cell * lv.nBnd );
+   const int cell = blk / lv.nChunks;
    if ( cell >= lv.nCells )
       return;
-   const HbBndPoint p   = lv.bnd[i];
-   const HbRegion   reg = lv.cells[cell].region[p.mask];
+   const HbBndChunk  ch  = lv.chunks[blk - cell * lv.nChunks];
+   const HbCellInfo* ci  = lv.cells + cell;
+   const HbRegion    reg = ci->region[ch.mask];
    if ( !( a.bc.type[reg.bflag] & a.flag ) )
       return;
    if ( !( ( a.dimSel >> reg.dim ) & 1 ) )
       return;
-   if ( a.bndColour >= 0 && hb_interface_colour( lv.cells[cell], lv.N, p.x, p.y, p.z ) != a.bndColour )
+   if ( (int) threadIdx.x >= ch.count )
+      return;
+   const int        i = ch.first + threadIdx.x;
+   const HbBndPoint p = lv.bnd[i];
+   if ( a.bndColour >= 0 && hb_interface_colour( *ci, lv.N, p.x, p.y, p.z ) != a.bndColour )
       return;
    double sNb, diag;
-   hb_boundary_stencil( lv, a.W, a.src, cell, p.x, p.y, p.z, sNb, diag );
-   const size_t gi     = (size_t) cell * lv.cellSize + hb_index( lv.N, p.x, p.y, p.z );
-   const double centre = a.src[cell][gi - (size_t) cell * lv.cellSize];
-   double*      out    = a.toScratch ? ( a.scratch + item ) : ( a.dst + gi );
+   hb_boundary_stencil( lv, a.W, a.src, ci, ch.mask, p.x, p.y, p.z, sNb, diag );
+   const size_t local  = (size_t) hb_index( lv.N, p.x, p.y, p.z );
+   const size_t gi     = (size_t) cell * lv.cellSize + local;
+   const double centre = a.src[cell][local];
+   double*      out    = a.toScratch ? ( a.scratch + (size_t) cell * lv.nBnd + i ) : ( a.dst + gi );
    hb_epilogue< MODE >( a, out, gi, sNb, diag, centre );
 }
 
@@ -160,10 +166,7 @@ __global__ void __launch_bounds__( HB_BLOCK )
       hb_interior_tile< MODE >( lv, a, cell, t, threadIdx.x >> 5, threadIdx.x & 31 );
    }
    else if ( doBoundary )
-   {
-      const long long item = (long long) ( b - nInteriorBlocks ) * blockDim.x + threadIdx.x;
-      hb_boundary_item< MODE >( lv, a, item );
-   }
+      hb_boundary_block< MODE >( lv, a, b - nInteriorBlocks );
 }
 
 // scratch -> dst for the interface phases of SOR
@@ -189,8 +192,7 @@ template < int MODE >
 static void hb_launch_stencil_mode( const HbLevelView& lv, const HbStencilArgs& a, bool interior, bool boundary, cudaStream_t st )
 {
    const long long nIntBlocks = interior ? (long long) lv.nCells * lv.nTiles : 0;
-   const long long nBndItems  = boundary ? (long long) lv.nCells * lv.nBnd : 0;
-   const long long nBndBlocks = ( nBndItems + HB_BLOCK - 1 ) / HB_BLOCK;
+   const long long nBndBlocks = boundary ? (long long) lv.nCells * lv.nChunks : 0;
    const long long grid       = nIntBlocks + nBndBlocks;
    if ( grid == 0 )
       return;

@@ -1,6 +1,7 @@
 // C-ABI implementation, part 1: runtime, PrimitiveStorage tables, P1Function storage and BLAS-1.
 #include "runtime.hpp"
 
+#include <algorithm>
 #include <cstring>
 
 #include "../../include/hyteg_b200.h"
@@ -72,10 +73,12 @@ void hb_storage::uploadTopologyTables()
    view.build( topo, view.rank, view.nRanks );
    dCells.upload( view.cells );
    dCopies.upload( view.copies );
+   dRegionCopies.upload( view.regionCopies );
    for ( auto& kv : levels )
    {
       kv.second->view.cells  = dCells.ptr;
       kv.second->view.copies = dCopies.ptr;
+      kv.second->view.regionCopies = dRegionCopies.ptr;
       kv.second->view.nSlots = (int) view.slotGlobal.size();
    }
    tablesDirty = false;
@@ -124,6 +127,23 @@ hb::LevelTables& hb_storage::level( int L )
             t.pad = 0;
             tiles.push_back( t );
          }
+   // interface points grouped by region (mask), lexicographic inside a region; chunks of <= 256 points of one region
+   std::stable_sort( bnd.begin(), bnd.end(), []( const HbBndPoint& a, const HbBndPoint& b ) { return a.mask < b.mask; } );
+   std::vector< HbBndChunk > chunks;
+   for ( size_t i = 0; i < bnd.size(); )
+   {
+      size_t j = i;
+      while ( j < bnd.size() && bnd[j].mask == bnd[i].mask && j - i < 256 )
+         j++;
+      HbBndChunk c;
+      c.first = (int32_t) i;
+      c.count = (int32_t) ( j - i );
+      c.mask  = bnd[i].mask;
+      c.pad   = 0;
+      chunks.push_back( c );
+      i = j;
+   }
+   lt->chunks.upload( chunks );
    lt->bnd.upload( bnd );
    lt->xyz.upload( lt->hXyz );
    lt->mask.upload( mask );
@@ -151,6 +171,9 @@ hb::LevelTables& hb_storage::level( int L )
    v.tiles        = lt->tiles.ptr;
    v.cells        = dCells.ptr;
    v.copies       = dCopies.ptr;
+   v.regionCopies = dRegionCopies.ptr;
+   v.chunks       = lt->chunks.ptr;
+   v.nChunks      = (int) chunks.size();
    auto& ref      = *lt;
    levels[L]      = std::move( lt );
    return ref;

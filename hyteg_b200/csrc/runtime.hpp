@@ -55,6 +55,7 @@ struct LevelTables
    DeviceBuffer< HbBndPoint > bnd, xyz;
    DeviceBuffer< uint8_t >    mask;
    DeviceBuffer< HbTile >     tiles;
+   DeviceBuffer< HbBndChunk > chunks;
    DeviceBuffer< HbItem >     items;   // work items of the TMA-streamed interior kernel
    DeviceBuffer< HbItem >     itemsShuffle; // work items of the centre-column + shuffle interior kernel
    DeviceBuffer< double >     scratch; // nCells*nBnd, interface staging (SOR)
@@ -69,6 +70,7 @@ struct hb_storage
    hb::LocalView                            view;
    hb::DeviceBuffer< HbCellInfo >           dCells;
    hb::DeviceBuffer< HbCopy >               dCopies;
+   hb::DeviceBuffer< HbRegionCopy >         dRegionCopies;
    std::map< int, std::unique_ptr< hb::LevelTables > > levels;
    hb::DeviceBuffer< double >               reducePartial; // HB_REDUCE_MAX_BLOCKS
    hb::DeviceBuffer< double >               reduceOut;     // 8 slots

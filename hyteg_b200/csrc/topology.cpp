@@ -196,6 +196,7 @@ void LocalView::build( const Topology& topo, int rank_, int nRanks_ )
 
    cells.assign( nLocal, HbCellInfo{} );
    copies.clear();
+   regionCopies.clear();
    auto fillRegions = [&topo]( HbCellInfo& ci, int c ) {
       ci.globalId = c;
       for ( int j = 0; j < 4; j++ )
@@ -270,6 +271,47 @@ void LocalView::build( const Topology& topo, int rank_, int nRanks_ )
          copies.push_back( cp );
       }
       ci.copyEnd = (int) copies.size();
+      // per interface region: the macro-cells that contain the primitive, with the coordinate map into each of them
+      for ( int m = 0; m <= HB_NMASK; m++ )
+         ci.rcBegin[m] = (int) regionCopies.size();
+      for ( int m = 1; m < HB_NMASK; m++ )
+      {
+         ci.rcBegin[m] = (int) regionCopies.size();
+         if ( ci.region[m].dim > 2 )
+            continue;
+         // support = local vertices with non-zero barycentric weight on the region; b0 <-> bit3, b1 <-> bit0, b2 <-> bit1, b3 <-> bit2
+         static const int faceBitOfB[4] = { 8, 1, 2, 4 };
+         int              supp          = 0;
+         for ( int j = 0; j < 4; j++ )
+            if ( !( m & faceBitOfB[j] ) )
+               supp |= 1 << j;
+         for ( int e = ci.copyBegin; e < ci.copyEnd; e++ )
+         {
+            const HbCopy& cp = copies[e];
+            if ( supp & ~cp.sharedMask )
+               continue;
+            HbRegionCopy rc{};
+            rc.slot = cp.slot;
+            // b = ( N-x-y-z, x, y, z ) as rows over ( N, x, y, z )
+            static const int bRow[4][4] = { { 1, -1, -1, -1 }, { 0, 1, 0, 0 }, { 0, 0, 1, 0 }, { 0, 0, 0, 1 } };
+            int              bp[4][4]   = { { 0 } };
+            bool             nz[4]      = { false, false, false, false };
+            for ( int j = 0; j < 4; j++ )
+               if ( ( supp >> j ) & 1 )
+               {
+                  const int k = cp.vmap[j];
+                  nz[k]       = true;
+                  for ( int t = 0; t < 4; t++ )
+                     bp[k][t] += bRow[j][t];
+               }
+            for ( int k = 1; k < 4; k++ )
+               for ( int t = 0; t < 4; t++ )
+                  rc.c[k - 1][t] = (int8_t) bp[k][t];
+            rc.maskp = (uint8_t) ( ( nz[1] ? 0 : 1 ) | ( nz[2] ? 0 : 2 ) | ( nz[3] ? 0 : 4 ) | ( nz[0] ? 0 : 8 ) );
+            regionCopies.push_back( rc );
+         }
+      }
+      ci.rcBegin[HB_NMASK] = (int) regionCopies.size();
    }
    // region tables of the mirrored (remote) cells: needed for multiplicities in the grid transfer
    cells.resize( slotGlobal.size(), HbCellInfo{} );

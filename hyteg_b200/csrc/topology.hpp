@@ -58,6 +58,7 @@ struct LocalView
    std::map< int, int > globalToSlot;
    std::vector< HbCellInfo > cells;        // [nLocal] (region tables + copy ranges)
    std::vector< HbCopy >     copies;
+   std::vector< HbRegionCopy > regionCopies;
 
    void build( const Topology& topo, int rank, int nRanks );
 };
