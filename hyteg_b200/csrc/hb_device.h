@@ -85,6 +85,7 @@ enum HbMode
 struct HbStencilArgs
 {
    const double* const* src; // cell pointer table (owned + mirrored cells) used for stencil reads
+   const double*        srcBase; // arena of the source function: owned cell c starts at srcBase + c * cellSize
    const double*        W;   // [nSlots][16][15]
    double*              dst; // local arena
    const double*        rhs; // local arena
@@ -92,6 +93,7 @@ struct HbStencilArgs
    double*              scratch; // [nCells*nBnd] staging for interface phases (SOR)
    double               omega;
    int32_t              flag;    // DoFType selection
+   uint32_t             selMask; // bit f set: primitives with meshBoundaryFlag f are selected ( bc.type[f] & flag )
    int32_t              colour;  // SOR colour 0..3 (interior)
    int32_t              dimSel;  // boundary phase: bitmask of primitive dims to process (1<<dim)
    int32_t              toScratch; // boundary results go to scratch instead of dst
@@ -136,6 +138,7 @@ __device__ __forceinline__ void
 __device__ __forceinline__ void hb_boundary_stencil( const HbLevelView&   lv,
                                                      const double*        W,
                                                      const double* const* src,
+                                                     const double*        srcBase,
                                                      const HbCellInfo*    ci,
                                                      int                  mask,
                                                      int                  x,
@@ -155,7 +158,8 @@ __device__ __forceinline__ void hb_boundary_stencil( const HbLevelView&   lv,
       const int          yp = rc.c[1][0] * N + rc.c[1][1] * x + rc.c[1][2] * y + rc.c[1][3] * z;
       const int          zp = rc.c[2][0] * N + rc.c[2][1] * x + rc.c[2][2] * y + rc.c[2][3] * z;
       const double* __restrict__ w = W + ( (size_t) rc.slot * HB_NMASK + rc.maskp ) * HB_NDIR;
-      const double* __restrict__ s = src[rc.slot];
+      // owned cells: pointer arithmetic (one dependent load less); mirrored cells of other ranks: pointer table
+      const double* __restrict__ s = rc.slot < lv.nCells ? srcBase + (size_t) rc.slot * lv.cellSize : src[rc.slot];
       const int                  vm = hb_valid[rc.maskp];
       // linear index of the image point and the index deltas of the six (dy,dz) row changes of the 15-point stencil
       const int ws   = N + 1 - zp;                // width of slice zp

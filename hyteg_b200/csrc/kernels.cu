@@ -64,7 +64,7 @@ __device__ __forceinline__ void hb_interior_tile( const HbLevelView& lv, const H
       return;
 
    const HbRegion reg = lv.cells[cell].region[0];
-   if ( !( a.bc.type[reg.bflag] & a.flag ) )
+   if ( !( ( a.selMask >> reg.bflag ) & 1 ) )
       return;
 
    const double* S = a.src[cell];
@@ -132,7 +132,7 @@ __device__ __forceinline__ void hb_boundary_block( const HbLevelView& lv, const 
    const HbBndChunk  ch  = lv.chunks[blk - cell * lv.nChunks];
    const HbCellInfo* ci  = lv.cells + cell;
    const HbRegion    reg = ci->region[ch.mask];
-   if ( !( a.bc.type[reg.bflag] & a.flag ) )
+   if ( !( ( a.selMask >> reg.bflag ) & 1 ) )
       return;
    if ( !( ( a.dimSel >> reg.dim ) & 1 ) )
       return;
@@ -143,10 +143,10 @@ __device__ __forceinline__ void hb_boundary_block( const HbLevelView& lv, const 
    if ( a.bndColour >= 0 && hb_interface_colour( *ci, lv.N, p.x, p.y, p.z ) != a.bndColour )
       return;
    double sNb, diag;
-   hb_boundary_stencil( lv, a.W, a.src, ci, ch.mask, p.x, p.y, p.z, sNb, diag );
+   hb_boundary_stencil( lv, a.W, a.src, a.srcBase, ci, ch.mask, p.x, p.y, p.z, sNb, diag );
    const size_t local  = (size_t) hb_index( lv.N, p.x, p.y, p.z );
    const size_t gi     = (size_t) cell * lv.cellSize + local;
-   const double centre = a.src[cell][local];
+   const double centre = a.srcBase[gi];
    double*      out    = a.toScratch ? ( a.scratch + (size_t) cell * lv.nBnd + i ) : ( a.dst + gi );
    hb_epilogue< MODE >( a, out, gi, sNb, diag, centre );
 }
@@ -169,6 +169,14 @@ __global__ void __launch_bounds__( HB_BLOCK )
       hb_boundary_block< MODE >( lv, a, b - nInteriorBlocks );
 }
 
+// Interface points only (large levels: the interior runs in its own streaming kernel).  Small register budget so that four
+// CTAs are resident per SM: the kernel is a chain of dependent table look-ups and gathers, i.e. latency-bound.
+template < int MODE >
+__global__ void __launch_bounds__( HB_BLOCK, 4 ) hb_interface_kernel( const HbLevelView lv, const HbStencilArgs a )
+{
+   hb_boundary_block< MODE >( lv, a, blockIdx.x );
+}
+
 // scratch -> dst for the interface phases of SOR
 __global__ void hb_commit_kernel( const HbLevelView lv, const HbStencilArgs a )
 {
@@ -179,7 +187,7 @@ __global__ void hb_commit_kernel( const HbLevelView lv, const HbStencilArgs a )
    const int        i   = (int) ( item - (long long) cell * lv.nBnd );
    const HbBndPoint p   = lv.bnd[i];
    const HbRegion   reg = lv.cells[cell].region[p.mask];
-   if ( !( a.bc.type[reg.bflag] & a.flag ) )
+   if ( !( ( a.selMask >> reg.bflag ) & 1 ) )
       return;
    if ( !( ( a.dimSel >> reg.dim ) & 1 ) )
       return;
@@ -196,6 +204,11 @@ static void hb_launch_stencil_mode( const HbLevelView& lv, const HbStencilArgs& 
    const long long grid       = nIntBlocks + nBndBlocks;
    if ( grid == 0 )
       return;
+   if ( nIntBlocks == 0 )
+   {
+      HB_LAUNCH( hb_interface_kernel< MODE >, (unsigned) grid, HB_BLOCK, st, lv, a );
+      return;
+   }
    HB_LAUNCH( hb_stencil_kernel< MODE >, (unsigned) grid, HB_BLOCK, st, lv, a, (int) nIntBlocks, boundary ? 1 : 0 );
 }
 
