@@ -152,7 +152,7 @@ hb::LevelTables& hb_storage::level( int L )
       std::vector< HbItem > items;
       hb_stream_build_items( N, items );
       lt->items.upload( items );
-      hb_shuffle_build_items( N, items );
+      hb_shuffle_build_items( N, items, hb::tuning( "shuffle_ys", 0 ), hb::tuning( "shuffle_order", 0 ) );
       lt->itemsShuffle.upload( items );
    }
    lt->scratch.alloc( (size_t) view.nLocal * bnd.size() );

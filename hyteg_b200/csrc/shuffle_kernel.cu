@@ -21,6 +21,7 @@
 #ifndef HB_EMUL
 
 #include <cstdint>
+#include <type_traits>
 
 namespace {
 
@@ -51,24 +52,23 @@ struct ModeTraits
    static constexpr bool hasExtra = ( MODE != HB_APPLY_REPLACE );
 };
 
+// value stored at the output point; Ax = full stencil sum, e = fused operand (dst / rhs / x), centre = src at the point
 template < int MODE >
-__device__ __forceinline__ void epilogue( const HbStencilArgs& a, size_t gi, double Ax, double invd, double centre, double e )
+__device__ __forceinline__ double epilogue( const HbStencilArgs& a, double Ax, double invd, double centre, double e )
 {
-   if ( MODE == HB_APPLY_REPLACE )
-      a.dst[gi] = Ax;
-   else if ( MODE == HB_APPLY_ADD )
-      a.dst[gi] = e + Ax;
-   else if ( MODE == HB_RESIDUAL )
-      a.dst[gi] = e - Ax;
-   else if ( MODE == HB_JACOBI )
-      a.dst[gi] = centre + a.omega * ( invd * ( e - Ax ) );
-   else if ( MODE == HB_CHEB_FIRST )
-      a.dst[gi] = invd * ( e - Ax );
-   else if ( MODE == HB_CHEB_STEP )
-   {
-      a.dst[gi] = invd * Ax;
-      a.aux[gi] = e + a.omega * centre;
-   }
+   if ( MODE == HB_APPLY_ADD )
+      return e + Ax;
+   if ( MODE == HB_RESIDUAL )
+      return e - Ax;
+   if ( MODE == HB_JACOBI )
+      return centre + a.omega * ( invd * ( e - Ax ) );
+   if ( MODE == HB_CHEB_FIRST )
+      return invd * ( e - Ax );
+   if ( MODE == HB_SOR ) // e = rhs; Ax includes the centre term: invd * ( rhs - sum over neighbours ) = invd * ( e - Ax ) + centre
+      return ( 1.0 - a.omega ) * centre + a.omega * ( invd * ( e - Ax ) + centre );
+   if ( MODE == HB_CHEB_STEP ) // second store ( aux = e + omega * centre ) is issued by the caller
+      return invd * Ax;
+   return Ax; // HB_APPLY_REPLACE
 }
 
 } // namespace
@@ -80,9 +80,18 @@ __global__ void __launch_bounds__( PAIRS * 32, 2 ) hb_shuffle_kernel( const HbLe
 {
    constexpr bool EX = ModeTraits< MODE >::hasExtra;
    const int      N  = lv.N;
-   // item-major order, items sorted by decreasing work: the last wave of CTAs consists of the smallest items
-   const int itemIdx = blockIdx.x / lv.nCells;
-   const int cell    = blockIdx.x - itemIdx * lv.nCells;
+   // item-major order: CTAs of consecutive block ids work on the same item of different macro-cells
+   int itemIdx, cell;
+   if ( sa.cellMajor )
+   {
+      cell    = blockIdx.x / sa.nItems;
+      itemIdx = blockIdx.x - cell * sa.nItems;
+   }
+   else
+   {
+      itemIdx = blockIdx.x / lv.nCells;
+      cell    = blockIdx.x - itemIdx * lv.nCells;
+   }
    if ( !( ( sa.selMask >> c_bflag[sa.constBase + cell] ) & 1 ) )
       return;
    const HbItem it   = sa.items[itemIdx];
@@ -92,66 +101,136 @@ __global__ void __launch_bounds__( PAIRS * 32, 2 ) hb_shuffle_kernel( const HbLe
       return;
    const int    xc       = it.x0 - 1 + lane; // this lane's column
    const size_t cellBase = (size_t) cell * lv.cellSize;
-   const double* __restrict__ S = sa.srcArena + cellBase;
-   const double* __restrict__ E = EX ? sa.extraArena + cellBase : nullptr;
 
    const double* w    = c_W[sa.constBase + cell];
    const double  invd = w[15]; // 1 / w[D_C], stored behind the 15 weights
 
-   const int yFirstIn = it.ya - 1;       // first input row
-   const int yLastIn  = it.ya + it.nOut; // last input row
-   // running indices: li[q] = (column xc, next row to LOAD) of slice zA-1+q; ei/oi = extra operand / output position
-   int li[4];
-#pragma unroll
-   for ( int q = 0; q < 4; q++ )
-      li[q] = row_base( N, yFirstIn, zA - 1 + q ) + xc;
-   int       yLoad = yFirstIn;
-   int       oi0 = row_base( N, yFirstIn - 1, zA ) + xc, oi1 = row_base( N, yFirstIn - 1, zA + 1 ) + xc; // output row of iteration 0
-   int       ei0 = oi0, ei1 = oi1;                                                                       // extra row to LOAD
-   int       yExtra = yFirstIn - 1;
-   const bool laneOut = ( lane >= 1 ) && ( lane <= XOUT );
-   const int  yMax0   = laneOut ? min( it.ya + it.nOut - 1, min( N - 2 - zA, N - 1 - zA - xc ) ) : -1;
-   const int  yMax1   = ( laneOut && zA + 1 <= N - 3 ) ? min( it.ya + it.nOut - 1, min( N - 3 - zA, N - 2 - zA - xc ) ) : -1;
+   // ---- addressing ------------------------------------------------------------------------------------------------
+   // Row pitch of slice z at row y is (N + 1 - z) - y.  With P pointing at (column xc, row y) of a slice whose pitch there is
+   // 'pitch', row y + j of the slice 'q' slices above starts 8 * ( j * pitch - j (j - 1) / 2 - q j ) bytes further: one
+   // IMAD.WIDE with an immediate multiplier per access plus an immediate offset, all accesses of an unrolled block
+   // independent of each other.  Addresses are opaque 64-bit integers and the accesses are PTX, so the compiler neither
+   // re-derives them from indices nor serialises them.
+   using u64       = unsigned long long;
+   const u64 srcB  = (u64) ( sa.srcArena + cellBase );
+   const u64 dstB  = (u64) ( a.dst + cellBase );
+   const u64 exB   = EX ? (u64) ( sa.extraArena + cellBase ) : 0ull;
+   const int ya    = it.ya, nOut = it.nOut;
+   const int rowIn = row_base( N, ya - 1, zA - 1 ) + xc; // slice zA-1, row ya-1
+   u64       P0    = srcB + 8ull * (u64) rowIn;
+   u64       P1    = srcB + 8ull * (u64) ( row_base( N, ya - 1, zA ) + xc );
+   u64       P2    = srcB + 8ull * (u64) ( row_base( N, ya - 1, zA + 1 ) + xc );
+   u64       P3    = srcB + 8ull * (u64) ( row_base( N, ya - 1, zA + 2 ) + xc );
+   int       ld    = ( N + 2 - zA ) - ( ya - 1 ); // pitch of slice zA-1 at the row the P's point to
+   const int oi0 = row_base( N, ya, zA ) + xc, oi1 = row_base( N, ya, zA + 1 ) + xc;
+   u64       O0 = dstB + 8ull * (u64) oi0, O1 = dstB + 8ull * (u64) oi1; // output row of the block's first iteration
+   u64       E0 = exB + 8ull * (u64) oi0, E1 = exB + 8ull * (u64) oi1;   // next row of the fused operand to load
+   int       so = ( N + 1 - zA ) - ya;                                   // pitch of slice zA at the row O0 / E0 point to
+   int       se = so;
+   const long long auxOff = ( MODE == HB_CHEB_STEP ) ? (long long) ( (u64) a.aux - (u64) a.dst ) : 0ll;
 
+   const bool laneOut = ( lane >= 1 ) && ( lane <= XOUT );
+   const int  yMax0   = laneOut ? min( ya + nOut - 1, min( N - 2 - zA, N - 1 - zA - xc ) ) : -1;
+   const int  yMax1   = ( laneOut && zA + 1 <= N - 3 ) ? min( ya + nOut - 1, min( N - 3 - zA, N - 2 - zA - xc ) ) : -1;
+   int        r0 = max( 0, yMax0 - ya + 1 ), r1 = max( 0, yMax1 - ya + 1 ); // rows this lane still has to store in slice zA / zA+1
+   // SOR: colour (x + 2y + 3z) mod 4 of the output point (same colouring as the generic kernel); k0 == 0 mod 4 <=> slice zA matches
+   int k0 = ( MODE == HB_SOR ) ? ( xc + 2 * ya + 3 * zA - a.colour ) : 0;
+
+   auto rowAddr = [&]( u64 P, int pitch, int j, int q ) -> u64 { return P + (u64) ( (long long) pitch * ( 8 * j ) + (long long) ( -8 * ( j * ( j - 1 ) / 2 + q * j ) ) ); };
+   auto load    = [&]( double& v, u64 addr, bool pred ) {
+      if ( MODE == HB_SOR ) // SOR updates the array it reads (only points of other colours matter): coherent loads
+         asm volatile( "{\n .reg .pred p;\n setp.ne.s32 p, %2, 0;\n @p ld.global.f64 %0, [%1];\n}" : "+d"( v ) : "l"( addr ), "r"( (int) pred ) : "memory" );
+      else
+         asm( "{\n .reg .pred p;\n setp.ne.s32 p, %2, 0;\n @p ld.global.nc.f64 %0, [%1];\n}" : "+d"( v ) : "l"( addr ), "r"( (int) pred ) );
+   };
+   auto loadNow = [&]( double& v, u64 addr ) {
+      if ( MODE == HB_SOR )
+         asm volatile( "ld.global.f64 %0, [%1];" : "=d"( v ) : "l"( addr ) : "memory" );
+      else
+         asm( "ld.global.nc.f64 %0, [%1];" : "=d"( v ) : "l"( addr ) );
+   };
+   auto store = [&]( u64 addr, double v, bool pred ) {
+      asm volatile( "{\n .reg .pred p;\n setp.ne.s32 p, %2, 0;\n @p st.global.f64 [%0], %1;\n}" ::"l"( addr ), "d"( v ), "r"( (int) pred ) : "memory" );
+   };
+
+   // ---- prologue: window rows ya-1 (A) and ya (B), then the ring: rows ya+1 .. ya+DEPTH (and the fused operand of rows ya ..) ----
+   double B0, A1, B1, A2, B2, A3, B3;
+   loadNow( A1, rowAddr( P1, ld, 0, 1 ) );
+   loadNow( A2, rowAddr( P2, ld, 0, 2 ) );
+   loadNow( A3, rowAddr( P3, ld, 0, 3 ) );
+   loadNow( B0, rowAddr( P0, ld, 1, 0 ) );
+   loadNow( B1, rowAddr( P1, ld, 1, 1 ) );
+   loadNow( B2, rowAddr( P2, ld, 1, 2 ) );
+   loadNow( B3, rowAddr( P3, ld, 1, 3 ) );
    double pf[DEPTH][4];
    double pe[DEPTH][2];
-   auto   loadRow = [&]( double ( &dst )[4], double ( &de )[2] ) {
-      const bool ok = yLoad <= yLastIn;
-#pragma unroll
-      for ( int q = 0; q < 4; q++ )
-      {
-         dst[q] = ok ? __ldg( S + li[q] ) : 0.0;
-         li[q] += ( N + 2 - zA - q ) - yLoad; // next row of slice zA-1+q
-      }
-      if ( EX )
-      {
-         const bool oke = ( yExtra >= it.ya ) && ( yExtra < yLastIn );
-         de[0]          = ( oke && yExtra <= yMax0 ) ? E[ei0] : 0.0;
-         de[1]          = ( oke && yExtra <= yMax1 ) ? E[ei1] : 0.0;
-         ei0 += ( N + 1 - zA ) - yExtra;
-         ei1 += ( N - zA ) - yExtra;
-      }
-      yLoad++;
-      yExtra++;
-   };
+   int    nLoad = nOut; // ring rows still to load: ya+1 .. ya+nOut
 #pragma unroll
    for ( int d = 0; d < DEPTH; d++ )
-      loadRow( pf[d], pe[d] );
-
-   // register window (centre column only): slice q rows A (y-1), B (y)
-   double B0 = 0, A1 = 0, B1 = 0, A2 = 0, B2 = 0, A3 = 0, B3 = 0;
-   int    yo = yFirstIn - 1; // output row of the current iteration
-   const int nIn = it.nOut + 2;
-   for ( int base = 0; base < nIn; base += DEPTH )
    {
+      pf[d][0] = pf[d][1] = pf[d][2] = pf[d][3] = 0.0;
+      pe[d][0] = pe[d][1] = 0.0;
+      const bool ok = d < nLoad;
+      load( pf[d][0], rowAddr( P0, ld, 2 + d, 0 ), ok );
+      load( pf[d][1], rowAddr( P1, ld, 2 + d, 1 ), ok );
+      load( pf[d][2], rowAddr( P2, ld, 2 + d, 2 ), ok );
+      load( pf[d][3], rowAddr( P3, ld, 2 + d, 3 ), ok );
+      if ( EX )
+      {
+         load( pe[d][0], rowAddr( E0, se, d, 0 ), ok );
+         load( pe[d][1], rowAddr( E1, se, d, 1 ), ok );
+      }
+   }
+   P0 = rowAddr( P0, ld, 2 + DEPTH, 0 );
+   P1 = rowAddr( P1, ld, 2 + DEPTH, 1 );
+   P2 = rowAddr( P2, ld, 2 + DEPTH, 2 );
+   P3 = rowAddr( P3, ld, 2 + DEPTH, 3 );
+   ld -= 2 + DEPTH;
+   if ( EX )
+   {
+      E0 = rowAddr( E0, se, DEPTH, 0 );
+      E1 = rowAddr( E1, se, DEPTH, 1 );
+      se -= DEPTH;
+   }
+   nLoad -= DEPTH;
+
+   // one unrolled block of DEPTH output rows; guarded = the refill loads test nLoad (tail of the item), otherwise unconditional
+   auto block = [&]( auto guarded ) {
+      constexpr bool G  = decltype( guarded )::value;
+      const int      km = k0 & 3;
 #pragma unroll
       for ( int u = 0; u < DEPTH; u++ )
       {
          const double N0 = pf[u][0], N1 = pf[u][1], N2 = pf[u][2], N3 = pf[u][3];
-         const double e0 = pe[u][0], e1 = pe[u][1];
-         loadRow( pf[u], pe[u] ); // refill the slot: row DEPTH ahead
+         const double x0 = pe[u][0], x1 = pe[u][1];
+         // refill the slot: row DEPTH ahead
+         if ( G )
+         {
+            const bool ok = u < nLoad;
+            load( pf[u][0], rowAddr( P0, ld, u, 0 ), ok );
+            load( pf[u][1], rowAddr( P1, ld, u, 1 ), ok );
+            load( pf[u][2], rowAddr( P2, ld, u, 2 ), ok );
+            load( pf[u][3], rowAddr( P3, ld, u, 3 ), ok );
+            if ( EX )
+            {
+               load( pe[u][0], rowAddr( E0, se, u, 0 ), ok );
+               load( pe[u][1], rowAddr( E1, se, u, 1 ), ok );
+            }
+         }
+         else
+         {
+            loadNow( pf[u][0], rowAddr( P0, ld, u, 0 ) );
+            loadNow( pf[u][1], rowAddr( P1, ld, u, 1 ) );
+            loadNow( pf[u][2], rowAddr( P2, ld, u, 2 ) );
+            loadNow( pf[u][3], rowAddr( P3, ld, u, 3 ) );
+            if ( EX )
+            {
+               loadNow( pe[u][0], rowAddr( E0, se, u, 0 ) );
+               loadNow( pe[u][1], rowAddr( E1, se, u, 1 ) );
+            }
+         }
 
-         // output (zA, yo): below = slice 0, own = 1, above = 2
+         // output (zA, y): below = slice 0, own = 1, above = 2
          double c0 = w[D_C] * B1;
          c0        = fma( w[D_N], N1, c0 );
          c0        = fma( w[D_S], A1, c0 );
@@ -163,11 +242,11 @@ __global__ void __launch_bounds__( PAIRS * 32, 2 ) hb_shuffle_kernel( const HbLe
          l0        = fma( w[D_NW], N1, l0 );
          l0        = fma( w[D_BNW], N0, l0 );
          l0        = fma( w[D_TW], B2, l0 );
-         double r0 = w[D_E] * B1;
-         r0        = fma( w[D_SE], A1, r0 );
-         r0        = fma( w[D_BE], B0, r0 );
-         r0        = fma( w[D_TSE], A2, r0 );
-         // output (zA+1, yo): below = slice 1, own = 2, above = 3
+         double r0v = w[D_E] * B1;
+         r0v        = fma( w[D_SE], A1, r0v );
+         r0v        = fma( w[D_BE], B0, r0v );
+         r0v        = fma( w[D_TSE], A2, r0v );
+         // output (zA+1, y): below = slice 1, own = 2, above = 3
          double c1 = w[D_C] * B2;
          c1        = fma( w[D_N], N2, c1 );
          c1        = fma( w[D_S], A2, c1 );
@@ -179,18 +258,28 @@ __global__ void __launch_bounds__( PAIRS * 32, 2 ) hb_shuffle_kernel( const HbLe
          l1        = fma( w[D_NW], N2, l1 );
          l1        = fma( w[D_BNW], N1, l1 );
          l1        = fma( w[D_TW], B3, l1 );
-         double r1 = w[D_E] * B2;
-         r1        = fma( w[D_SE], A2, r1 );
-         r1        = fma( w[D_BE], B1, r1 );
-         r1        = fma( w[D_TSE], A3, r1 );
+         double r1v = w[D_E] * B2;
+         r1v        = fma( w[D_SE], A2, r1v );
+         r1v        = fma( w[D_BE], B1, r1v );
+         r1v        = fma( w[D_TSE], A3, r1v );
 
-         const double Ax0 = c0 + __shfl_up_sync( 0xffffffffu, l0, 1 ) + __shfl_down_sync( 0xffffffffu, r0, 1 );
-         const double Ax1 = c1 + __shfl_up_sync( 0xffffffffu, l1, 1 ) + __shfl_down_sync( 0xffffffffu, r1, 1 );
+         const double Ax0 = c0 + __shfl_up_sync( 0xffffffffu, l0, 1 ) + __shfl_down_sync( 0xffffffffu, r0v, 1 );
+         const double Ax1 = c1 + __shfl_up_sync( 0xffffffffu, l1, 1 ) + __shfl_down_sync( 0xffffffffu, r1v, 1 );
 
-         if ( yo >= it.ya && yo <= yMax0 )
-            epilogue< MODE >( a, cellBase + oi0, Ax0, invd, B1, e0 );
-         if ( yo >= it.ya && yo <= yMax1 )
-            epilogue< MODE >( a, cellBase + oi1, Ax1, invd, B2, e1 );
+         bool s0 = u < r0, s1 = u < r1;
+         if ( MODE == HB_SOR )
+         {
+            s0 = s0 && ( km == ( ( 4 - 2 * u ) & 3 ) );
+            s1 = s1 && ( km == ( ( 1 - 2 * u ) & 3 ) ); // k0 + 3 + 2u == 0 mod 4
+         }
+         const u64 q0 = rowAddr( O0, so, u, 0 ), q1 = rowAddr( O1, so, u, 1 );
+         store( q0, epilogue< MODE >( a, Ax0, invd, B1, x0 ), s0 );
+         store( q1, epilogue< MODE >( a, Ax1, invd, B2, x1 ), s1 );
+         if ( MODE == HB_CHEB_STEP )
+         {
+            store( q0 + (u64) auxOff, x0 + a.omega * B1, s0 );
+            store( q1 + (u64) auxOff, x1 + a.omega * B2, s1 );
+         }
 
          // slide the window
          B0 = N0;
@@ -200,11 +289,35 @@ __global__ void __launch_bounds__( PAIRS * 32, 2 ) hb_shuffle_kernel( const HbLe
          B2 = N2;
          A3 = B3;
          B3 = N3;
-         oi0 += ( N + 1 - zA ) - yo;
-         oi1 += ( N - zA ) - yo;
-         yo++;
       }
+      P0 = rowAddr( P0, ld, DEPTH, 0 );
+      P1 = rowAddr( P1, ld, DEPTH, 1 );
+      P2 = rowAddr( P2, ld, DEPTH, 2 );
+      P3 = rowAddr( P3, ld, DEPTH, 3 );
+      ld -= DEPTH;
+      O0 = rowAddr( O0, so, DEPTH, 0 );
+      O1 = rowAddr( O1, so, DEPTH, 1 );
+      so -= DEPTH;
+      if ( EX )
+      {
+         E0 = rowAddr( E0, se, DEPTH, 0 );
+         E1 = rowAddr( E1, se, DEPTH, 1 );
+         se -= DEPTH;
+      }
+      r0 -= DEPTH;
+      r1 -= DEPTH;
+      nLoad -= DEPTH;
+      if ( MODE == HB_SOR )
+         k0 += 2 * DEPTH;
+   };
+   int left = nOut; // output rows still to produce
+   while ( nLoad >= DEPTH )
+   {
+      block( std::false_type{} );
+      left -= DEPTH;
    }
+   for ( ; left > 0; left -= DEPTH )
+      block( std::true_type{} );
 }
 
 } // namespace
@@ -234,7 +347,7 @@ bool hb_shuffle_supported( int mode, const HbLevelView& lv )
    if ( lv.N < 32 || lv.nCells == 0 || lv.nCells > HB_CONST_W_ENTRIES )
       return false;
    return mode == HB_APPLY_REPLACE || mode == HB_APPLY_ADD || mode == HB_RESIDUAL || mode == HB_JACOBI || mode == HB_CHEB_FIRST ||
-          mode == HB_CHEB_STEP;
+          mode == HB_CHEB_STEP || mode == HB_SOR;
 }
 
 template < int DEPTH >
@@ -260,6 +373,9 @@ static void launchDepth( int mode, unsigned g, unsigned b, const HbLevelView& lv
    case HB_CHEB_STEP:
       hb_shuffle_kernel< HB_CHEB_STEP, DEPTH ><<< g, b, 0, st >>>( lv, a, sa );
       break;
+   case HB_SOR:
+      hb_shuffle_kernel< HB_SOR, DEPTH ><<< g, b, 0, st >>>( lv, a, sa );
+      break;
    default:
       throw std::runtime_error( "hyteg_b200: mode not supported by the shuffle kernel" );
    }
@@ -271,25 +387,28 @@ void hb_launch_shuffle_stencil( int mode, const HbLevelView& lv, const HbStencil
    if ( grid < 1 )
       return;
    const unsigned g = (unsigned) grid, b = PAIRS * 32;
+   if ( depth <= 0 ) // fused-operand modes keep two more ring values per row: one row less in flight fits 128 registers
+      depth = ( mode == HB_APPLY_REPLACE ) ? DEPTH_DEFAULT : 4;
    switch ( depth )
    {
    case 3:
       launchDepth< 3 >( mode, g, b, lv, a, sa, st );
       break;
+   case 4:
+      launchDepth< 4 >( mode, g, b, lv, a, sa, st );
+      break;
    case 7:
       launchDepth< 7 >( mode, g, b, lv, a, sa, st );
-      break;
-   case 9:
-      launchDepth< 9 >( mode, g, b, lv, a, sa, st );
       break;
    default:
       launchDepth< DEPTH_DEFAULT >( mode, g, b, lv, a, sa, st );
    }
 }
 
-void hb_shuffle_build_items( int N, std::vector< HbItem >& items )
+void hb_shuffle_build_items( int N, std::vector< HbItem >& items, int ys, int order )
 {
-   const int ZBh = 2 * PAIRS, YS = 45;
+   // ys + 2 input rows per item: a multiple of DEPTH_DEFAULT keeps the last unrolled block full
+   const int ZBh = 2 * PAIRS, YS = ys > 0 ? ys : 48;
    items.clear();
    std::vector< long long > work;
    for ( int z0 = 1; z0 <= N - 3; z0 += ZBh )
@@ -311,7 +430,12 @@ void hb_shuffle_build_items( int N, std::vector< HbItem >& items )
       const int nz = std::min( 2 * PAIRS, N - 2 - it.z0 );
       return (long long) ( it.nOut + 2 + DEPTH_DEFAULT ) * ( ( nz + 1 ) / 2 );
    };
-   std::stable_sort( items.begin(), items.end(), [&]( const HbItem& a, const HbItem& b ) { return cost( a ) > cost( b ); } );
+   if ( order == 2 ) // x fastest: consecutive CTAs read neighbouring column chunks of the same rows
+      std::stable_sort( items.begin(), items.end(), []( const HbItem& a, const HbItem& b ) {
+         return a.z0 != b.z0 ? a.z0 < b.z0 : ( a.ya != b.ya ? a.ya < b.ya : a.x0 < b.x0 );
+      } );
+   if ( order == 0 )
+      std::stable_sort( items.begin(), items.end(), [&]( const HbItem& a, const HbItem& b ) { return cost( a ) > cost( b ); } );
 }
 
 #else // HB_EMUL
@@ -321,7 +445,7 @@ bool hb_shuffle_supported( int, const HbLevelView& )
    return false;
 }
 void hb_launch_shuffle_stencil( int, const HbLevelView&, const HbStencilArgs&, const HbStreamArgs&, cudaStream_t, int ) {}
-void hb_shuffle_build_items( int, std::vector< HbItem >& items )
+void hb_shuffle_build_items( int, std::vector< HbItem >& items, int, int )
 {
    items.clear();
 }

@@ -1,0 +1,29 @@
+"""Interior-kernel sweep over item order / grid mapping (run plain for times, or under ncu for DRAM bytes)."""
+import os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+import hyteg_b200 as hb
+from hyteg_b200 import api, meshes
+L = 8
+lib = hb.get_lib(); lib.check(lib.dll.hb_device_init(0))
+s = torch.cuda.current_stream(); lib.dll.hb_set_stream(s.cuda_stream)
+v, c = meshes.cube_6el()
+reps = int(sys.argv[1]) if len(sys.argv) > 1 else 20
+def t(fn, n=reps):
+    for _ in range(2): fn()
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record(s)
+    for _ in range(n): fn()
+    b.record(s); torch.cuda.synchronize()
+    return a.elapsed_time(b) / n * 1e3
+lib.dll.hb_set_tuning(b"apply_parts", 1)
+for order in (0, 1, 2):
+    for cm in (0, 1):
+        lib.dll.hb_set_tuning(b"shuffle_order", order); lib.dll.hb_set_tuning(b"shuffle_cell_major", cm)
+        st = api.PrimitiveStorage(v, c); st.setMeshBoundaryFlagsOnBoundary(1, 0, True)
+        A = api.P1ConstantLaplaceOperator(st, L, L)
+        src, dst = api.P1Function("s", st, L, L), api.P1Function("d", st, L, L)
+        src.interpolate(1.0, L, hb.All)
+        print("order", order, "cell_major", cm, "interior %.1f us" % t(lambda: A.apply(src, dst, L, hb.All)), flush=True)
+        del A, src, dst, st
