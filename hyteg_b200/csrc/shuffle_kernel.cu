@@ -75,8 +75,8 @@ __device__ __forceinline__ double epilogue( const HbStencilArgs& a, double Ax, d
 
 namespace {
 
-template < int MODE, int DEPTH >
-__global__ void __launch_bounds__( PAIRS * 32, 2 ) hb_shuffle_kernel( const HbLevelView lv, const HbStencilArgs a, const HbStreamArgs sa )
+template < int MODE, int DEPTH, int REGS = 128 >
+__global__ void __maxnreg__( REGS ) hb_shuffle_kernel( const HbLevelView lv, const HbStencilArgs a, const HbStreamArgs sa )
 {
    constexpr bool EX = ModeTraits< MODE >::hasExtra;
    const int      N  = lv.N;
@@ -112,7 +112,8 @@ __global__ void __launch_bounds__( PAIRS * 32, 2 ) hb_shuffle_kernel( const HbLe
    // independent of each other.  Addresses are opaque 64-bit integers and the accesses are PTX, so the compiler neither
    // re-derives them from indices nor serialises them.
    using u64       = unsigned long long;
-   const u64 srcB  = (u64) ( sa.srcArena + cellBase );
+   // sa.sync bits 1,2 are measurement probes (tools/sweep_order.py): all cells read macro-cell 0 / nothing is stored
+   const u64 srcB  = (u64) ( sa.srcArena + ( ( sa.sync & 2 ) ? 0 : cellBase ) );
    const u64 dstB  = (u64) ( a.dst + cellBase );
    const u64 exB   = EX ? (u64) ( sa.extraArena + cellBase ) : 0ull;
    const int ya    = it.ya, nOut = it.nOut;
@@ -132,7 +133,7 @@ __global__ void __launch_bounds__( PAIRS * 32, 2 ) hb_shuffle_kernel( const HbLe
    const bool laneOut = ( lane >= 1 ) && ( lane <= XOUT );
    const int  yMax0   = laneOut ? min( ya + nOut - 1, min( N - 2 - zA, N - 1 - zA - xc ) ) : -1;
    const int  yMax1   = ( laneOut && zA + 1 <= N - 3 ) ? min( ya + nOut - 1, min( N - 3 - zA, N - 2 - zA - xc ) ) : -1;
-   int        r0 = max( 0, yMax0 - ya + 1 ), r1 = max( 0, yMax1 - ya + 1 ); // rows this lane still has to store in slice zA / zA+1
+   int        r0 = ( sa.sync & 4 ) ? 0 : max( 0, yMax0 - ya + 1 ), r1 = ( sa.sync & 4 ) ? 0 : max( 0, yMax1 - ya + 1 ); // rows this lane still has to store in slice zA / zA+1
    // SOR: colour (x + 2y + 3z) mod 4 of the output point (same colouring as the generic kernel); k0 == 0 mod 4 <=> slice zA matches
    int k0 = ( MODE == HB_SOR ) ? ( xc + 2 * ya + 3 * zA - a.colour ) : 0;
 
@@ -311,8 +312,12 @@ __global__ void __launch_bounds__( PAIRS * 32, 2 ) hb_shuffle_kernel( const HbLe
          k0 += 2 * DEPTH;
    };
    int left = nOut; // output rows still to produce
+   // optional CTA-wide pacing: the warps of a CTA share input slices pairwise, keeping them on the same rows keeps those in L1
+   const int nSync = ( sa.sync & 1 ) ? 32 * min( PAIRS, ( N - 3 - it.z0 ) / 2 + 1 ) : 0;
    while ( nLoad >= DEPTH )
    {
+      if ( nSync )
+         asm volatile( "bar.sync 1, %0;" ::"r"( nSync ) : "memory" );
       block( std::false_type{} );
       left -= DEPTH;
    }
@@ -350,9 +355,26 @@ bool hb_shuffle_supported( int mode, const HbLevelView& lv )
           mode == HB_CHEB_STEP || mode == HB_SOR;
 }
 
-template < int DEPTH >
-static void launchDepth( int mode, unsigned g, unsigned b, const HbLevelView& lv, const HbStencilArgs& a, const HbStreamArgs& sa, cudaStream_t st )
+// experimental register budgets (more resident CTAs per SM): apply and Jacobi only
+template < int DEPTH, int REGS >
+static bool launchRegs( int mode, unsigned g, unsigned b, const HbLevelView& lv, const HbStencilArgs& a, const HbStreamArgs& sa, cudaStream_t st )
 {
+   if ( mode == HB_APPLY_REPLACE )
+      hb_shuffle_kernel< HB_APPLY_REPLACE, DEPTH, REGS ><<< g, b, 0, st >>>( lv, a, sa );
+   else if ( mode == HB_JACOBI )
+      hb_shuffle_kernel< HB_JACOBI, DEPTH, REGS ><<< g, b, 0, st >>>( lv, a, sa );
+   else
+      return false;
+   return true;
+}
+
+template < int DEPTH >
+static void launchDepth( int mode, unsigned g, unsigned b, const HbLevelView& lv, const HbStencilArgs& a, const HbStreamArgs& sa, cudaStream_t st, int regs = 0 )
+{
+   if ( DEPTH <= 5 && regs == 1 && launchRegs< ( DEPTH <= 5 ? DEPTH : 3 ), 96 >( mode, g, b, lv, a, sa, st ) )
+      return;
+   if ( DEPTH <= 5 && regs == 2 && launchRegs< ( DEPTH <= 5 ? DEPTH : 3 ), 80 >( mode, g, b, lv, a, sa, st ) )
+      return;
    switch ( mode )
    {
    case HB_APPLY_REPLACE:
@@ -387,21 +409,23 @@ void hb_launch_shuffle_stencil( int mode, const HbLevelView& lv, const HbStencil
    if ( grid < 1 )
       return;
    const unsigned g = (unsigned) grid, b = PAIRS * 32;
+   const int regs = depth / 100; // tuning: 100 * register-budget code + depth
+   depth %= 100;
    if ( depth <= 0 ) // fused-operand modes keep two more ring values per row: one row less in flight fits 128 registers
       depth = ( mode == HB_APPLY_REPLACE ) ? DEPTH_DEFAULT : 4;
    switch ( depth )
    {
    case 3:
-      launchDepth< 3 >( mode, g, b, lv, a, sa, st );
+      launchDepth< 3 >( mode, g, b, lv, a, sa, st, regs );
       break;
    case 4:
-      launchDepth< 4 >( mode, g, b, lv, a, sa, st );
+      launchDepth< 4 >( mode, g, b, lv, a, sa, st, regs );
       break;
    case 7:
       launchDepth< 7 >( mode, g, b, lv, a, sa, st );
       break;
    default:
-      launchDepth< DEPTH_DEFAULT >( mode, g, b, lv, a, sa, st );
+      launchDepth< DEPTH_DEFAULT >( mode, g, b, lv, a, sa, st, regs );
    }
 }
 

@@ -24,6 +24,7 @@ struct HbStreamArgs
    int32_t       nItems;
    uint32_t      selMask; // bit f set: macro primitives with meshBoundaryFlag f are selected by (bc, flag)
    int32_t       constBase;                        // shuffle kernel: first entry of this level's weights in constant memory
+   int32_t       sync;      // shuffle kernel: pace the warps of a CTA with a named barrier per unrolled block
    int32_t       cellMajor; // shuffle kernel: block id = cell * nItems + item (else item * nCells + cell)
    int32_t*      counter; // [2] work counter + finished-CTA counter, both zero between launches
 };

@@ -1,4 +1,4 @@
-"""Interior-kernel sweep over item order / grid mapping (run plain for times, or under ncu for DRAM bytes)."""
+"""Interior-kernel sweep over item height / CTA pacing (run plain for times, or under ncu for DRAM bytes)."""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
@@ -18,12 +18,16 @@ def t(fn, n=reps):
     b.record(s); torch.cuda.synchronize()
     return a.elapsed_time(b) / n * 1e3
 lib.dll.hb_set_tuning(b"apply_parts", 1)
-for order in (0, 1, 2):
-    for cm in (0, 1):
-        lib.dll.hb_set_tuning(b"shuffle_order", order); lib.dll.hb_set_tuning(b"shuffle_cell_major", cm)
+for ys in (48,):
+    for sync in (0, 6):
+        lib.dll.hb_set_tuning(b"shuffle_ys", ys); lib.dll.hb_set_tuning(b"shuffle_sync", sync)
         st = api.PrimitiveStorage(v, c); st.setMeshBoundaryFlagsOnBoundary(1, 0, True)
         A = api.P1ConstantLaplaceOperator(st, L, L)
         src, dst = api.P1Function("s", st, L, L), api.P1Function("d", st, L, L)
         src.interpolate(1.0, L, hb.All)
-        print("order", order, "cell_major", cm, "interior %.1f us" % t(lambda: A.apply(src, dst, L, hb.All)), flush=True)
+        r = []
+        for depth in (4, 5, 103, 104, 105, 203, 204, 205):
+            lib.dll.hb_set_tuning(b"shuffle_depth", depth)
+            r.append("d%d %.1f us" % (depth, t(lambda: A.apply(src, dst, L, hb.All))))
+        print("ys", ys, "sync", sync, *r, flush=True)
         del A, src, dst, st

@@ -33,6 +33,10 @@ for ys in yss:
         for parts in (2, 3):
             lib.dll.hb_set_tuning(b"apply_parts", parts)
             print("   apply_parts", parts, "%.1f us" % t(lambda: A.apply(src, dst, L, hb.All)))
+        for ov, dep in ((1, 0), (1, 105), (1, 203)):
+            lib.dll.hb_set_tuning(b"overlap", ov); lib.dll.hb_set_tuning(b"shuffle_depth", dep)
+            print("   overlap", ov, "depth", dep, "apply %.1f us" % t(lambda: A.apply(src, dst, L, hb.All)))
+        lib.dll.hb_set_tuning(b"overlap", 0); lib.dll.hb_set_tuning(b"shuffle_depth", 0)
         for depth in (3, 4, 5):
             lib.dll.hb_set_tuning(b"shuffle_depth", depth)
             print("   depth", depth, "jacobi %.1f us" % t(lambda: A.smooth_jac(dst, rhs, src, 0.66, L, hb.SMOOTH_FLAG)),
