@@ -69,6 +69,13 @@ class PrimitiveStorage:
     def num_global_dofs(self, level):
         return int(self.lib.dll.hb_storage_num_global_dofs(self.h, level))
 
+    def exchange_info(self, level):
+        """(neighbouring ranks, doubles sent, doubles received) of one ghost exchange on `level`."""
+        n = C.c_int(0)
+        a, b = C.c_longlong(0), C.c_longlong(0)
+        self.lib.check(self.lib.dll.hb_storage_exchange_info(self.h, level, C.byref(n), C.byref(a), C.byref(b)))
+        return n.value, a.value, b.value
+
     def micro_coordinates(self, level):
         n = self.num_local_cells * self.cell_array_size(level)
         xyz = np.zeros((n, 3))
@@ -114,6 +121,10 @@ class P1Function:
         out = np.zeros(self._n(level))
         self.lib.check(self.lib.dll.hb_p1function_download(self.h, level, as_dp(out)))
         return out
+
+    def communicate(self, level):
+        """explicit ghost exchange (operators do it themselves when needed)"""
+        self.lib.check(self.lib.dll.hb_p1function_communicate(self.h, level))
 
     def device_ptr(self, level):
         return self.lib.dll.hb_p1function_device_ptr(self.h, level)

@@ -31,6 +31,13 @@ _SIGNATURES = {
     "hb_synchronize": (C.c_int, []),
     "hb_set_allreduce": (C.c_int, [_vp, _vp]),
     "hb_set_tuning": (C.c_int, [C.c_char_p, C.c_int]),
+    "hb_nccl_unique_id": (C.c_int, [_vp]),
+    "hb_nccl_init": (C.c_int, [_vp, C.c_int, C.c_int]),
+    "hb_nccl_finalize": (C.c_int, []),
+    "hb_set_exchange": (C.c_int, [_vp, _vp]),
+    "hb_exchange_stats": (C.c_int, [C.POINTER(C.c_longlong), C.POINTER(C.c_longlong)]),
+    "hb_storage_exchange_info": (C.c_int, [_vp, C.c_int, _ip, C.POINTER(C.c_longlong), C.POINTER(C.c_longlong)]),
+    "hb_p1function_communicate": (C.c_int, [_vp, C.c_int]),
     "hb_storage_create": (_vp, [C.c_int, _dp, C.c_int, _ip, C.c_int, C.c_int]),
     "hb_storage_destroy": (None, [_vp]),
     "hb_storage_set_mesh_boundary_flags_on_boundary": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int]),

@@ -435,6 +435,37 @@ void hb_launch_reduce( const HbLevelView& lv, const HbBC& bc, int flag, int op, 
 }
 
 // =============================================================================================
+//  Ghost exchange: pack the layers a peer needs into a contiguous send buffer / unpack a received buffer into the
+//  mirrored macro-cells (reference: VertexDoFPackInfo::packDataForMacroFace / unpack..., communication/BufferedCommunication.cpp)
+// =============================================================================================
+
+__global__ void hb_pack_kernel( const double* arena, const long long* off, long long n, double* buf )
+{
+   const long long stride = (long long) gridDim.x * blockDim.x;
+   for ( long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride )
+      buf[i] = arena[off[i]];
+}
+
+__global__ void hb_unpack_kernel( double* arena, const long long* off, long long n, const double* buf )
+{
+   const long long stride = (long long) gridDim.x * blockDim.x;
+   for ( long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride )
+      arena[off[i]] = buf[i];
+}
+
+void hb_launch_pack( const double* arena, const long long* off, long long n, double* buf, cudaStream_t st )
+{
+   if ( n > 0 )
+      HB_LAUNCH( hb_pack_kernel, hb_flat_grid( (size_t) n, 256, 148 * 8 ), 256, st, arena, off, n, buf );
+}
+
+void hb_launch_unpack( double* arena, const long long* off, long long n, const double* buf, cudaStream_t st )
+{
+   if ( n > 0 )
+      HB_LAUNCH( hb_unpack_kernel, hb_flat_grid( (size_t) n, 256, 148 * 8 ), 256, st, arena, off, n, buf );
+}
+
+// =============================================================================================
 //  Grid transfer (gather form)
 // =============================================================================================
 

@@ -28,3 +28,6 @@ void hb_launch_multelem( const HbLevelView& lv, const HbLinComb& lc, cudaStream_
 void hb_launch_reduce( const HbLevelView& lv, const HbBC& bc, int flag, int op, const double* a, const double* b, double* partial, double* out, cudaStream_t st );
 void hb_launch_restrict( const HbLevelView& coarse, const HbLevelView& fine, const double* const* fsrc, double* cdst, const HbBC& bc, int flag, cudaStream_t st );
 void hb_launch_prolongate( const HbLevelView& coarse, const HbLevelView& fine, const double* csrc, double* fdst, const HbBC& bc, int flag, int add, cudaStream_t st );
+// ghost exchange: buf[i] = arena[off[i]] / arena[off[i]] = buf[i]
+void hb_launch_pack( const double* arena, const long long* off, long long n, double* buf, cudaStream_t st );
+void hb_launch_unpack( double* arena, const long long* off, long long n, const double* buf, cudaStream_t st );

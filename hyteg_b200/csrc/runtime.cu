@@ -179,6 +179,73 @@ hb::LevelTables& hb_storage::level( int L )
    return ref;
 }
 
+// Ghost exchange tables of a level: for every plan entry the sorted union of the layers of its regions, where the layer of
+// region m is the set of points of the macro-cell within stencil distance 1 of the region (the region itself included).
+hb::LevelTables::Exchange& hb_storage::exchange( int L )
+{
+   hb::LevelTables&           lt = level( L );
+   hb::LevelTables::Exchange& ex = lt.ex;
+   if ( ex.built )
+      return ex;
+   const int N = lt.view.N;
+   std::vector< std::vector< int > > layer( HB_NMASK );
+   for ( const HbBndPoint& p : lt.hXyz )
+   {
+      if ( p.mask == 0 )
+         continue;
+      for ( int d = 0; d < HB_NDIR; d++ )
+      {
+         const int x = p.x + hb::kDir[d][0], y = p.y + hb::kDir[d][1], z = p.z + hb::kDir[d][2];
+         if ( x < 0 || y < 0 || z < 0 || x + y + z > N )
+            continue;
+         layer[p.mask].push_back( hb_index( N, x, y, z ) );
+      }
+   }
+   for ( auto& l : layer )
+   {
+      std::sort( l.begin(), l.end() );
+      l.erase( std::unique( l.begin(), l.end() ), l.end() );
+   }
+   auto offsets = [&]( const std::vector< hb::LocalView::ExchangeEntry >& plan, std::vector< long long >& off, std::vector< long long >& start ) {
+      off.clear();
+      start.assign( ex.peers.size() + 1, 0 );
+      for ( size_t k = 0; k < ex.peers.size(); k++ )
+      {
+         start[k] = (long long) off.size();
+         for ( const auto& e : plan )
+         {
+            if ( e.peer != ex.peers[k] )
+               continue;
+            std::vector< int > u;
+            for ( int m = 1; m < HB_NMASK; m++ )
+               if ( ( e.masks >> m ) & 1 )
+                  u.insert( u.end(), layer[m].begin(), layer[m].end() );
+            std::sort( u.begin(), u.end() );
+            u.erase( std::unique( u.begin(), u.end() ), u.end() );
+            for ( int i : u )
+               off.push_back( (long long) e.slot * lt.view.cellSize + i );
+         }
+      }
+      start[ex.peers.size()] = (long long) off.size();
+   };
+   ex.peers.clear();
+   for ( const auto& e : view.sendPlan )
+      ex.peers.push_back( e.peer );
+   for ( const auto& e : view.recvPlan )
+      ex.peers.push_back( e.peer );
+   std::sort( ex.peers.begin(), ex.peers.end() );
+   ex.peers.erase( std::unique( ex.peers.begin(), ex.peers.end() ), ex.peers.end() );
+   std::vector< long long > so, ro;
+   offsets( view.sendPlan, so, ex.sendStart );
+   offsets( view.recvPlan, ro, ex.recvStart );
+   ex.sendOff.upload( so );
+   ex.recvOff.upload( ro );
+   ex.sendBuf.alloc( so.size() );
+   ex.recvBuf.alloc( ro.size() );
+   ex.built = true;
+   return ex;
+}
+
 extern "C" {
 
 const char* hb_last_error( void )
@@ -390,5 +457,6 @@ int hb_storage_micro_coordinates( const hb_storage* cst, int level, double* xyz 
 
 } // extern "C"
 
+#include "runtime_comm.inc"
 #include "runtime_function.inc"
 #include "runtime_operator.inc"

@@ -60,6 +60,17 @@ struct LevelTables
    DeviceBuffer< HbItem >     itemsShuffle; // work items of the centre-column + shuffle interior kernel
    DeviceBuffer< double >     scratch; // nCells*nBnd, interface staging (SOR)
    std::vector< HbBndPoint >  hXyz;    // host copy of the coordinate template
+
+   // ghost exchange of this level (n_ranks > 1, built on first use): element offsets into a function arena
+   // ( slot * cellSize + local index ), grouped by peer in the order of LocalView::sendPlan / recvPlan
+   struct Exchange
+   {
+      bool                         built = false;
+      std::vector< int >           peers;                // ranks this rank exchanges with (ascending)
+      std::vector< long long >     sendStart, recvStart; // [nPeers+1] ranges in sendOff / recvOff
+      DeviceBuffer< long long >    sendOff, recvOff;
+      DeviceBuffer< double >       sendBuf, recvBuf;
+   } ex;
 };
 
 } // namespace hb
@@ -79,6 +90,7 @@ struct hb_storage
    bool                                     tablesDirty = true;
 
    hb::LevelTables& level( int L );
+   hb::LevelTables::Exchange& exchange( int L ); // builds the level's exchange tables on first use
    void             uploadTopologyTables();
    ~hb_storage();
 };
@@ -90,6 +102,9 @@ struct hb_function
    HbBC        bc;
    std::vector< hb::DeviceBuffer< double > >  data;    // per level: local arena
    std::vector< hb::DeviceBuffer< double* > > cellPtr; // per level: [nSlots] device pointers
+   std::vector< char > mirrorsStale;                   // per level: mirrored cells do not hold the owners' current values
+   void touched( int L ) { mirrorsStale[L - minLevel] = 1; } // call after every write to the level's arena
+   void syncMirrors( int L );                                // ghost exchange if stale (no-op on one rank)
    double*        arena( int L ) const;
    double* const* ptrs( int L ) const;
    void           check( int L ) const;

@@ -180,6 +180,46 @@ void Topology::regionPrimitive( int cell, int mask, int& dim, int& id ) const
    }
 }
 
+uint32_t sharedRegionMasks( const Topology& topo, int g, int rank )
+{
+   static const int faceBitOfB[4] = { 8, 1, 2, 4 }; // local vertex j is OFF the face with this mask bit
+   uint32_t         out           = 0;
+   for ( int m = 1; m < HB_NMASK - 1; m++ )
+   {
+      int dim, id;
+      topo.regionPrimitive( g, m, dim, id );
+      if ( dim > 2 )
+         continue;
+      // cells of 'rank' around the first support vertex that contain all support vertices
+      int supp[4], ns = 0;
+      for ( int j = 0; j < 4; j++ )
+         if ( !( m & faceBitOfB[j] ) )
+            supp[ns++] = topo.cellV[g][j];
+      bool found = false;
+      for ( int c : topo.vCells[supp[0]] )
+      {
+         if ( c == g || topo.cellRank[c] != rank )
+            continue;
+         bool all = true;
+         for ( int k = 1; k < ns && all; k++ )
+         {
+            bool has = false;
+            for ( int j = 0; j < 4; j++ )
+               has = has || topo.cellV[c][j] == supp[k];
+            all = has;
+         }
+         if ( all )
+         {
+            found = true;
+            break;
+         }
+      }
+      if ( found )
+         out |= 1u << m;
+   }
+   return out;
+}
+
 void LocalView::build( const Topology& topo, int rank_, int nRanks_ )
 {
    rank   = rank_;
@@ -317,6 +357,33 @@ void LocalView::build( const Topology& topo, int rank_, int nRanks_ )
    cells.resize( slotGlobal.size(), HbCellInfo{} );
    for ( size_t sl = (size_t) nLocal; sl < slotGlobal.size(); sl++ )
       fillRegions( cells[sl], slotGlobal[sl] );
+
+   // ghost exchange plan
+   sendPlan.clear();
+   recvPlan.clear();
+   if ( nRanks > 1 )
+   {
+      for ( int peer = 0; peer < nRanks; peer++ )
+      {
+         if ( peer == rank )
+            continue;
+         for ( int c = 0; c < topo.nC; c++ ) // ascending global id
+         {
+            if ( topo.cellRank[c] == rank )
+            {
+               const uint32_t m = sharedRegionMasks( topo, c, peer );
+               if ( m )
+                  sendPlan.push_back( ExchangeEntry{ peer, globalToSlot.at( c ), m } );
+            }
+            else if ( topo.cellRank[c] == peer )
+            {
+               const uint32_t m = sharedRegionMasks( topo, c, rank );
+               if ( m )
+                  recvPlan.push_back( ExchangeEntry{ peer, globalToSlot.at( c ), m } );
+            }
+         }
+      }
+   }
 }
 
 } // namespace hb

@@ -60,7 +60,23 @@ struct LocalView
    std::vector< HbCopy >     copies;
    std::vector< HbRegionCopy > regionCopies;
 
+   // Ghost exchange plan (n_ranks > 1), level independent part.  A rank needs, of a remote macro-cell g, the values within
+   // stencil distance 1 of every macro primitive (face / edge / vertex) g shares with one of the rank's own cells:
+   // 'masks' has bit m set for every such region m of g.  Sender and receiver derive the same entries in the same order
+   // (by peer rank, then by global cell id) from the topology alone, so no handshake is needed.  This is the role of
+   // HyTeG's communicate< Cell, Face >() ... ghost-layer updates (reference communication/BufferedCommunication.cpp:181-420).
+   struct ExchangeEntry
+   {
+      int      peer;  // remote rank
+      int      slot;  // send: owned slot, recv: mirrored slot
+      uint32_t masks; // regions of the cell whose layers travel
+   };
+   std::vector< ExchangeEntry > sendPlan, recvPlan;
+
    void build( const Topology& topo, int rank, int nRanks );
 };
+
+// bit m set <=> some macro-cell owned by 'rank' contains the macro primitive 'region m' of macro-cell g
+uint32_t sharedRegionMasks( const Topology& topo, int g, int rank );
 
 } // namespace hb

@@ -55,6 +55,22 @@ int         hb_synchronize( void );
  * op: 0 sum, 2 max.  buf is a HOST buffer of n doubles. */
 typedef void ( *hb_allreduce_fn )( double* buf, int n, int op, void* ctx );
 int hb_set_allreduce( hb_allreduce_fn fn, void* ctx );
+/* ---- ranks: macro-cells are partitioned over n_ranks processes (one per GPU); the ghost layers next to macro primitives
+ * shared between ranks are exchanged on demand before every operation that reads them.  Stands in for HyTeG's
+ * communicate< From, To >() (src/hyteg/communication/BufferedCommunication.cpp:181-420, VertexDoFPackInfo.hpp).
+ * Product path: NCCL send/recv over NVLink on the library's stream.  Rank 0 calls hb_nccl_unique_id, the host plumbing
+ * (MPI / torch.distributed) broadcasts the 128 bytes, every rank calls hb_nccl_init; dotGlobal then all-reduces on the
+ * device as well.  NCCL is bound at run time (dlopen), the library has no link-time dependency on it. */
+int hb_nccl_unique_id( void* id128 );
+int hb_nccl_init( const void* id128, int rank, int n_ranks );
+int hb_nccl_finalize( void );
+/* Alternative for hosts without NCCL (CPU tests over gloo/MPI): called with the packed send buffers of every neighbouring
+ * rank and the receive buffers to fill; buffers live where function data lives (device memory in the product build). */
+typedef int ( *hb_exchange_fn )( void* ctx, int n_peers, const int* peers, double* const* send, const long long* n_send,
+                                 double* const* recv, const long long* n_recv, void* stream );
+int hb_set_exchange( hb_exchange_fn fn, void* ctx );
+/* number of ghost exchanges done so far and doubles sent by this rank (all functions, all levels) */
+int hb_exchange_stats( long long* calls, long long* doubles_sent );
 /* tuning knobs for kernel experiments: "tile_rows" */
 int hb_set_tuning( const char* key, int value );
 
@@ -80,6 +96,9 @@ long long hb_storage_num_global_dofs( const hb_storage* st, int level );
 /* coordinates of every entry of the local arena on 'level': xyz[3 * n_local_cells * cell_array_size] */
 int hb_storage_micro_coordinates( const hb_storage* st, int level, double* xyz );
 
+/* neighbouring ranks of this rank and the size of one ghost exchange of a function on 'level' */
+int hb_storage_exchange_info( hb_storage* st, int level, int* n_peers, long long* doubles_sent, long long* doubles_received );
+
 /* ---- P1Function  (src/hyteg/p1functionspace/VertexDoFFunction.hpp/.cpp) ------------------------- */
 hb_function* hb_p1function_create( hb_storage* st, int min_level, int max_level );
 void         hb_p1function_destroy( hb_function* f );
@@ -95,6 +114,8 @@ int hb_p1function_upload( hb_function* f, int level, const double* host, int fla
 int hb_p1function_download( const hb_function* f, int level, double* host );
 int hb_p1function_upload_cell( hb_function* f, int level, int local_cell, const double* host );
 int hb_p1function_download_cell( const hb_function* f, int level, int local_cell, double* host );
+/* explicit ghost exchange (communicate); operators call it themselves when the mirrored layers are stale */
+int hb_p1function_communicate( hb_function* f, int level );
 /* raw device pointer of the local arena (for zero-copy interop, e.g. torch tensors) */
 double* hb_p1function_device_ptr( hb_function* f, int level );
 /* interpolate( constant, level, flag ) */
