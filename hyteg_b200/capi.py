@@ -58,6 +58,8 @@ _SIGNATURES = {
     "hb_p1function_level_range": (C.c_int, [_vp, _ip, _ip]),
     "hb_p1function_upload": (C.c_int, [_vp, C.c_int, _dp, C.c_int]),
     "hb_p1function_download": (C.c_int, [_vp, C.c_int, _dp]),
+    "hb_p1function_upload_async": (C.c_int, [_vp, C.c_int, _dp]),
+    "hb_p1function_download_async": (C.c_int, [_vp, C.c_int, _dp]),
     "hb_p1function_upload_cell": (C.c_int, [_vp, C.c_int, C.c_int, _dp]),
     "hb_p1function_download_cell": (C.c_int, [_vp, C.c_int, C.c_int, _dp]),
     "hb_p1function_device_ptr": (_vp, [_vp, C.c_int]),

@@ -31,6 +31,16 @@ cudaStream_t currentStream()
    return g_stream;
 }
 
+StreamScope::StreamScope( cudaStream_t s )
+: saved( g_stream )
+{
+   g_stream = s;
+}
+StreamScope::~StreamScope()
+{
+   g_stream = saved;
+}
+
 int tuning( const std::string& key, int dflt )
 {
    auto it = g_tuning.find( key );

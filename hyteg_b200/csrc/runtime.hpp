@@ -18,6 +18,13 @@ namespace hb {
 void         cudaCheck( cudaError_t e, const char* what );
 cudaStream_t currentStream();
 int          tuning( const std::string& key, int dflt );
+// temporarily redirects the library's stream (ghost exchange on the side stream)
+struct StreamScope
+{
+   cudaStream_t saved;
+   explicit StreamScope( cudaStream_t s );
+   ~StreamScope();
+};
 
 template < typename T >
 struct DeviceBuffer

@@ -112,6 +112,9 @@ int hb_p1function_level_range( const hb_function* f, int* min_level, int* max_le
  * primitive matches 'flag' are written (interpolate semantics, VertexDoFFunction.cpp interpolate). */
 int hb_p1function_upload( hb_function* f, int level, const double* host, int flag );
 int hb_p1function_download( const hb_function* f, int level, double* host );
+/* stream-ordered copies of the whole local arena without a synchronize (host buffer pinned and kept alive by the caller) */
+int hb_p1function_upload_async( hb_function* f, int level, const double* host );
+int hb_p1function_download_async( const hb_function* f, int level, double* host );
 int hb_p1function_upload_cell( hb_function* f, int level, int local_cell, const double* host );
 int hb_p1function_download_cell( const hb_function* f, int level, int local_cell, double* host );
 /* explicit ghost exchange (communicate); operators call it themselves when the mirrored layers are stale */
