@@ -18,6 +18,9 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
+# dram__bytes_read.sum + dram__bytes_write.sum of one hb_shuffle_kernel<0,5,128> launch at level 8 on cube_6el
+# (ncu --set full capture, profiles/r1_b_apply_v3_ncu_full_summary.txt): 144.4 MB + 93.7 MB
+NCU_TRAFFIC_INTERIOR_L8 = 238.1e6
 BYTES_PER_DOF = {"apply": 16.0, "jacobi": 24.0, "sor": 24.0}  # algorithmic: src+dst / src+rhs+dst
 
 
@@ -234,6 +237,11 @@ def main():
     with ClockSampler(local) as clk:
         ms_apply = timed(apply_step, args.steps, W)
     ex0 = comm.exchange_stats(lib)
+    # the dominant kernel alone (interior points, hb_shuffle_kernel): tuning knob apply_parts = 1 launches only that kernel
+    lib.dll.hb_set_tuning(b"apply_parts", 1)
+    ms_interior = timed(lambda: A.apply(src, dst, L, hb.Inner), args.steps, W)
+    lib.dll.hb_set_tuning(b"apply_parts", 3)
+    n_interior = st.num_local_cells * ((2 ** L - 1) * (2 ** L - 2) * (2 ** L - 3) // 6)
     ms_jac = timed(lambda: A.smooth_jac(dst, rhs, src, 0.66, L, smooth), args.steps, W)
     ms_sor = timed(lambda: A.smooth_sor(dst, rhs, 1.0, L, smooth), max(args.steps // 5, 2), 3)
 
@@ -276,7 +284,8 @@ def main():
         peak, which = measured_peak()
         gd = lambda ms: ndof / (ms * 1e-3) / 1e9
         ndof_rank = ndof / world
-        achieved = BYTES_PER_DOF["apply"] * ndof_rank / (ms_apply * 1e-3) / 1e9
+        achieved = BYTES_PER_DOF["apply"] * n_interior / (ms_interior * 1e-3) / 1e9
+        whole = BYTES_PER_DOF["apply"] * ndof_rank / (ms_apply * 1e-3) / 1e9
         npeers, nsend, nrecv = st.exchange_info(L)
         line = {"metric": "P1 constant-stencil apply throughput", "value": gd(ms_apply), "unit": "GDoF/s", "n_gpus": world,
                 "steps": args.steps, "warmup": W, "ms_per_step": ms_apply, "higher_is_better": True, "scaling": "weak",
@@ -287,8 +296,12 @@ def main():
                            "l2": "src+dst arrays %.0f MB > 126 MB L2" % (2 * 8 * n_arr / 1e6),
                            "multi_gpu": "macro-cells partitioned, ghost layers over NCCL" if world > 1 else "single"},
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                             "traffic": 233.5e6 if L == 8 and world == 1 else None, "peak_source": which,
-                             "kernel": "hb_shuffle_kernel<APPLY_REPLACE> (interior) + hb_interface_kernel<APPLY_REPLACE>, one apply"},
+                             "traffic": NCU_TRAFFIC_INTERIOR_L8 if L == 8 else None, "peak_source": which,
+                             "kernel": "hb_shuffle_kernel<APPLY_REPLACE,5,128> (interior points of all local macro-cells, one launch)",
+                             "algorithmic_bytes_per_launch": BYTES_PER_DOF["apply"] * n_interior, "us_per_launch": 1e3 * ms_interior,
+                             "share_of_step": ms_interior / ms_apply,
+                             "whole_apply": {"achieved": whole, "frac": whole / peak,
+                                             "note": "16 B x all DoFs / apply time (interior + interface kernels, overlapped on two streams)"}},
                 "also": {"jacobi_gdofs": gd(ms_jac), "jacobi_frac": BYTES_PER_DOF["jacobi"] * ndof_rank / (ms_jac * 1e-3) / 1e9 / peak,
                          "sor_gdofs": gd(ms_sor), "sor_frac": BYTES_PER_DOF["sor"] * ndof_rank / (ms_sor * 1e-3) / 1e9 / peak,
                          "vcycle_3_3_gs_ms": ms_v, "ghost_exchanges_in_apply_region": ex0[0]},
