@@ -129,6 +129,15 @@ __device__ __forceinline__ void
       *out = 1.0 / diag;
 }
 
+// linear index, inside macro-cell rc.slot, of the image of the interface point (x,y,z) of the macro-cell the copy list belongs to
+__host__ __device__ __forceinline__ int hb_copy_index( int N, const HbRegionCopy& rc, int x, int y, int z )
+{
+   const int xp = rc.c[0][0] * N + rc.c[0][1] * x + rc.c[0][2] * y + rc.c[0][3] * z;
+   const int yp = rc.c[1][0] * N + rc.c[1][1] * x + rc.c[1][2] * y + rc.c[1][3] * z;
+   const int zp = rc.c[2][0] * N + rc.c[2][1] * x + rc.c[2][2] * y + rc.c[2][3] * z;
+   return hb_index( N, xp, yp, zp );
+}
+
 // Stencil at an interface point (x,y,z) of region 'mask' of macro-cell 'cell': sum of the partial stencils of every
 // macro-cell that contains the point, visited in ascending global cell id so that all copies of the point produce
 // bit-identical results.  The partial stencil of one cell is exactly HyTeG's calculateStencilInMacroCellForm_new

@@ -122,7 +122,9 @@ __device__ __forceinline__ void hb_interior_tile( const HbLevelView& lv, const H
 #undef HB_ROWBASE
 }
 
-// One block = one chunk (<= 256 points of ONE interface region) of one macro-cell.
+// One block = one chunk (<= 256 points of ONE interface region) of one macro-cell.  Only the rank-local owner of the macro
+// primitive (lowest macro-cell id on this rank) evaluates the stencil; the result goes to every copy of the point the rank holds
+// (all copies of a DoF hold identical values, so the owner's centre / rhs / dst operands stand for all of them).
 template < int MODE >
 __device__ __forceinline__ void hb_boundary_block( const HbLevelView& lv, const HbStencilArgs& a, int blk )
 {
@@ -132,6 +134,8 @@ __device__ __forceinline__ void hb_boundary_block( const HbLevelView& lv, const 
    const HbBndChunk  ch  = lv.chunks[blk - cell * lv.nChunks];
    const HbCellInfo* ci  = lv.cells + cell;
    const HbRegion    reg = ci->region[ch.mask];
+   if ( !( reg.owner & 2 ) )
+      return;
    if ( !( ( a.selMask >> reg.bflag ) & 1 ) )
       return;
    if ( !( ( a.dimSel >> reg.dim ) & 1 ) )
@@ -147,8 +151,25 @@ __device__ __forceinline__ void hb_boundary_block( const HbLevelView& lv, const 
    const size_t local  = (size_t) hb_index( lv.N, p.x, p.y, p.z );
    const size_t gi     = (size_t) cell * lv.cellSize + local;
    const double centre = a.srcBase[gi];
-   double*      out    = a.toScratch ? ( a.scratch + (size_t) cell * lv.nBnd + i ) : ( a.dst + gi );
-   hb_epilogue< MODE >( a, out, gi, sNb, diag, centre );
+   double       val;
+   hb_epilogue< MODE >( a, &val, gi, sNb, diag, centre ); // CHEB_STEP also updates aux[gi]
+   if ( a.toScratch )
+   {
+      a.scratch[(size_t) cell * lv.nBnd + i] = val; // fanned out by hb_commit_kernel
+      return;
+   }
+   const double auxVal = ( MODE == HB_CHEB_STEP ) ? a.aux[gi] : 0.0;
+   const int    e0 = ci->rcBegin[ch.mask], e1 = ci->rcBegin[ch.mask + 1];
+   for ( int e = e0; e < e1; e++ )
+   {
+      const HbRegionCopy rc = lv.regionCopies[e];
+      if ( rc.slot >= lv.nCells )
+         continue; // mirrored macro-cell of another rank: its owner computes the same value
+      const size_t gj = (size_t) rc.slot * lv.cellSize + (size_t) hb_copy_index( lv.N, rc, p.x, p.y, p.z );
+      a.dst[gj]       = val;
+      if ( MODE == HB_CHEB_STEP )
+         a.aux[gj] = auxVal;
+   }
 }
 
 // grid = nInteriorBlocks + nBoundaryBlocks.  Interior block b -> (cell, tile); its 8 warps take 8
@@ -177,23 +198,34 @@ __global__ void __launch_bounds__( HB_BLOCK, 4 ) hb_interface_kernel( const HbLe
    hb_boundary_block< MODE >( lv, a, blockIdx.x );
 }
 
-// scratch -> dst for the interface phases of SOR
+// scratch -> all local copies, for the interface phases of SOR
 __global__ void hb_commit_kernel( const HbLevelView lv, const HbStencilArgs a )
 {
    const long long item = (long long) blockIdx.x * blockDim.x + threadIdx.x;
    const int       cell = (int) ( item / lv.nBnd );
    if ( cell >= lv.nCells )
       return;
-   const int        i   = (int) ( item - (long long) cell * lv.nBnd );
-   const HbBndPoint p   = lv.bnd[i];
-   const HbRegion   reg = lv.cells[cell].region[p.mask];
+   const int         i   = (int) ( item - (long long) cell * lv.nBnd );
+   const HbBndPoint  p   = lv.bnd[i];
+   const HbCellInfo* ci  = lv.cells + cell;
+   const HbRegion    reg = ci->region[p.mask];
+   if ( !( reg.owner & 2 ) )
+      return;
    if ( !( ( a.selMask >> reg.bflag ) & 1 ) )
       return;
    if ( !( ( a.dimSel >> reg.dim ) & 1 ) )
       return;
-   if ( a.bndColour >= 0 && hb_interface_colour( lv.cells[cell], lv.N, p.x, p.y, p.z ) != a.bndColour )
+   if ( a.bndColour >= 0 && hb_interface_colour( *ci, lv.N, p.x, p.y, p.z ) != a.bndColour )
       return;
-   a.dst[(size_t) cell * lv.cellSize + hb_index( lv.N, p.x, p.y, p.z )] = a.scratch[item];
+   const double val = a.scratch[item];
+   const int    e0 = ci->rcBegin[p.mask], e1 = ci->rcBegin[p.mask + 1];
+   for ( int e = e0; e < e1; e++ )
+   {
+      const HbRegionCopy rc = lv.regionCopies[e];
+      if ( rc.slot >= lv.nCells )
+         continue;
+      a.dst[(size_t) rc.slot * lv.cellSize + (size_t) hb_copy_index( lv.N, rc, p.x, p.y, p.z )] = val;
+   }
 }
 
 template < int MODE >
@@ -264,7 +296,7 @@ __device__ __forceinline__ bool hb_point_selected( const HbLevelView& lv, const 
    const int local = (int) ( gi - (size_t) cell * lv.cellSize );
    const int m     = lv.mask[local];
    const HbRegion r = lv.cells[cell].region[m];
-   if ( ownerOnly && !r.owner )
+   if ( ownerOnly && !( r.owner & 1 ) )
       return false;
    return ( bc.type[r.bflag] & flag ) != 0;
 }

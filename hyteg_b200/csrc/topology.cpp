@@ -180,6 +180,35 @@ void Topology::regionPrimitive( int cell, int mask, int& dim, int& id ) const
    }
 }
 
+// lowest global id among the macro-cells of 'rank' that contain the macro primitive 'region m' of macro-cell g (-1: none)
+static int localMinCell( const Topology& topo, int g, int m, int rank )
+{
+   static const int faceBitOfB[4] = { 8, 1, 2, 4 };
+   int              supp[4], ns = 0;
+   for ( int j = 0; j < 4; j++ )
+      if ( !( m & faceBitOfB[j] ) )
+         supp[ns++] = topo.cellV[g][j];
+   if ( ns == 0 )
+      return -1;
+   int best = -1;
+   for ( int c : topo.vCells[supp[0]] ) // sorted ascending
+   {
+      if ( topo.cellRank[c] != rank )
+         continue;
+      bool all = true;
+      for ( int k = 1; k < ns && all; k++ )
+      {
+         bool has = false;
+         for ( int j = 0; j < 4; j++ )
+            has = has || topo.cellV[c][j] == supp[k];
+         all = has;
+      }
+      if ( all && ( best < 0 || c < best ) )
+         best = c;
+   }
+   return best;
+}
+
 uint32_t sharedRegionMasks( const Topology& topo, int g, int rank )
 {
    static const int faceBitOfB[4] = { 8, 1, 2, 4 }; // local vertex j is OFF the face with this mask bit
@@ -237,7 +266,7 @@ void LocalView::build( const Topology& topo, int rank_, int nRanks_ )
    cells.assign( nLocal, HbCellInfo{} );
    copies.clear();
    regionCopies.clear();
-   auto fillRegions = [&topo]( HbCellInfo& ci, int c ) {
+   auto fillRegions = [&topo, this]( HbCellInfo& ci, int c ) {
       ci.globalId = c;
       for ( int j = 0; j < 4; j++ )
          ci.gv[j] = topo.cellV[c][j];
@@ -274,6 +303,12 @@ void LocalView::build( const Topology& topo, int rank_, int nRanks_ )
             r.owner = 0;
             r.mult  = 1;
          }
+         // bit 0: owning copy over all ranks (every DoF counted once in dotGlobal); bit 1: owning copy on THIS rank -- that
+         // macro-cell evaluates the interface stencil and writes the result to all copies held by the rank
+         if ( dim == 3 )
+            r.owner = 3;
+         else if ( dim <= 2 && localMinCell( topo, c, m, rank ) == c )
+            r.owner |= 2;
       }
    };
    for ( int l = 0; l < nLocal; l++ )
