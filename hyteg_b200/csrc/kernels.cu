@@ -228,6 +228,117 @@ __global__ void hb_commit_kernel( const HbLevelView lv, const HbStencilArgs a )
    }
 }
 
+// Whole SOR sweep of a SMALL level in one launch: a single CTA walks the phases of hb_operator_smooth_sor (macro vertices,
+// edges in 2 colours, faces in 3 colours, each staged through scratch and committed; then the 4 interior colours) with a
+// block barrier in between.  The coarse levels of a V-cycle are launch-latency bound: 16 launches per sweep become one.
+// Same arithmetic, in the same order, as the multi-launch path (hb_boundary_block / hb_interior_tile).
+#ifndef HB_EMUL
+__global__ void __launch_bounds__( 1024 ) hb_sor_small_kernel( const HbLevelView lv, HbStencilArgs a, const int backwards )
+{
+   const int       N      = lv.N;
+   const long long nItems = (long long) lv.nCells * lv.nBnd;
+   const long long nAll   = (long long) lv.nCells * lv.cellSize;
+   auto interfacePhase = [&]( int dim, int colour ) {
+      for ( int pass = 0; pass < 2; pass++ ) // 0: evaluate into scratch, 1: commit to all local copies
+      {
+         for ( long long item = threadIdx.x; item < nItems; item += blockDim.x )
+         {
+            const int         cell = (int) ( item / lv.nBnd );
+            const int         i    = (int) ( item - (long long) cell * lv.nBnd );
+            const HbBndPoint  p    = lv.bnd[i];
+            const HbCellInfo* ci   = lv.cells + cell;
+            const HbRegion    reg  = ci->region[p.mask];
+            if ( !( reg.owner & 2 ) || reg.dim != dim || !( ( a.selMask >> reg.bflag ) & 1 ) )
+               continue;
+            if ( hb_interface_colour( *ci, N, p.x, p.y, p.z ) != colour )
+               continue;
+            if ( pass == 0 )
+            {
+               double sNb, diag;
+               hb_boundary_stencil( lv, a.W, a.src, a.srcBase, ci, p.mask, p.x, p.y, p.z, sNb, diag );
+               const size_t gi = (size_t) cell * lv.cellSize + (size_t) hb_index( N, p.x, p.y, p.z );
+               double       val;
+               hb_epilogue< HB_SOR >( a, &val, gi, sNb, diag, a.srcBase[gi] );
+               a.scratch[item] = val;
+            }
+            else
+            {
+               const double val = a.scratch[item];
+               for ( int e = ci->rcBegin[p.mask]; e < ci->rcBegin[p.mask + 1]; e++ )
+               {
+                  const HbRegionCopy rc = lv.regionCopies[e];
+                  if ( rc.slot < lv.nCells )
+                     a.dst[(size_t) rc.slot * lv.cellSize + (size_t) hb_copy_index( N, rc, p.x, p.y, p.z )] = val;
+               }
+            }
+         }
+         __syncthreads();
+      }
+   };
+   auto interiorPhase = [&]( int colour ) {
+      for ( long long g = threadIdx.x; g < nAll; g += blockDim.x )
+      {
+         const int        cell  = (int) ( g / lv.cellSize );
+         const int        local = (int) ( g - (long long) cell * lv.cellSize );
+         const HbBndPoint q     = lv.xyz[local];
+         if ( q.mask != 0 || ( ( q.x + 2 * q.y + 3 * q.z ) & 3 ) != colour )
+            continue;
+         if ( !( ( a.selMask >> lv.cells[cell].region[0].bflag ) & 1 ) )
+            continue;
+         const double* w = a.W + (size_t) cell * HB_NMASK * HB_NDIR;
+         const double* S = a.srcBase + (size_t) cell * lv.cellSize;
+         const int     x = q.x, y = q.y, z = q.z;
+         // same summation order as hb_interior_tile
+         double sum = w[D_W] * S[hb_index( N, x - 1, y, z )];
+         sum += w[D_E] * S[hb_index( N, x + 1, y, z )];
+         sum += w[D_N] * S[hb_index( N, x, y + 1, z )];
+         sum += w[D_NW] * S[hb_index( N, x - 1, y + 1, z )];
+         sum += w[D_S] * S[hb_index( N, x, y - 1, z )];
+         sum += w[D_SE] * S[hb_index( N, x + 1, y - 1, z )];
+         sum += w[D_BC] * S[hb_index( N, x, y, z - 1 )];
+         sum += w[D_BE] * S[hb_index( N, x + 1, y, z - 1 )];
+         sum += w[D_BN] * S[hb_index( N, x, y + 1, z - 1 )];
+         sum += w[D_BNW] * S[hb_index( N, x - 1, y + 1, z - 1 )];
+         sum += w[D_TC] * S[hb_index( N, x, y, z + 1 )];
+         sum += w[D_TW] * S[hb_index( N, x - 1, y, z + 1 )];
+         sum += w[D_TS] * S[hb_index( N, x, y - 1, z + 1 )];
+         sum += w[D_TSE] * S[hb_index( N, x + 1, y - 1, z + 1 )];
+         hb_epilogue< HB_SOR >( a, a.dst + g, (size_t) g, sum, w[D_C], S[local] );
+      }
+      __syncthreads();
+   };
+   const int nColours[3] = { 1, 2, 3 };
+   if ( !backwards )
+   {
+      for ( int d = 0; d <= 2; d++ )
+         for ( int c = 0; c < nColours[d]; c++ )
+            interfacePhase( d, c );
+      for ( int c = 0; c < 4; c++ )
+         interiorPhase( c );
+   }
+   else
+   {
+      for ( int c = 3; c >= 0; c-- )
+         interiorPhase( c );
+      for ( int d = 2; d >= 0; d-- )
+         for ( int c = nColours[d] - 1; c >= 0; c-- )
+            interfacePhase( d, c );
+   }
+}
+#endif
+
+bool hb_launch_sor_small( const HbLevelView& lv, const HbStencilArgs& a, int backwards, cudaStream_t st )
+{
+#ifdef HB_EMUL
+   return false;
+#else
+   if ( (long long) lv.nCells * lv.cellSize > 16384 )
+      return false; // more than 16 strided passes per interior colour: the multi-launch path wins
+   hb_sor_small_kernel<<< 1, 1024, 0, st >>>( lv, a, backwards );
+   return true;
+#endif
+}
+
 template < int MODE >
 static void hb_launch_stencil_mode( const HbLevelView& lv, const HbStencilArgs& a, bool interior, bool boundary, cudaStream_t st )
 {

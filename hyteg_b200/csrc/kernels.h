@@ -31,3 +31,5 @@ void hb_launch_prolongate( const HbLevelView& coarse, const HbLevelView& fine, c
 // ghost exchange: buf[i] = arena[off[i]] / arena[off[i]] = buf[i]
 void hb_launch_pack( const double* arena, const long long* off, long long n, double* buf, cudaStream_t st );
 void hb_launch_unpack( double* arena, const long long* off, long long n, const double* buf, cudaStream_t st );
+// whole SOR sweep of a small level in one single-CTA launch; false if the level is too large (or in the emulation build)
+bool hb_launch_sor_small( const HbLevelView& lv, const HbStencilArgs& a, int backwards, cudaStream_t st );

@@ -25,7 +25,17 @@
 
 namespace {
 
-constexpr int PAIRS = 8;  // warps per CTA = z-slice pairs per work item -> 16 output slices
+// CTA shape: ZP z-slice pairs x XCH column chunks = PAIRS warps.  More column chunks per CTA make the CTA's DRAM accesses
+// longer contiguous runs per row (XCH * 240 B), fewer z pairs cost more halo slices (2 ZP + 2 loaded per 2 ZP outputs).
+#ifndef HB_ZP
+#define HB_ZP 8
+#endif
+#ifndef HB_XCH
+#define HB_XCH 1
+#endif
+constexpr int ZP    = HB_ZP;
+constexpr int XCH   = HB_XCH;
+constexpr int PAIRS = ZP * XCH; // warps per CTA
 constexpr int XOUT  = 30; // output columns per warp
 constexpr int DEPTH_DEFAULT = 5; // rows in flight ahead of the row being computed (template parameter DEPTH)
 
@@ -96,10 +106,13 @@ __global__ void __maxnreg__( REGS ) hb_shuffle_kernel( const HbLevelView lv, con
       return;
    const HbItem it   = sa.items[itemIdx];
    const int    warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-   const int    zA   = it.z0 + 2 * warp; // this warp's output slices zA, zA+1
+   const int    zA   = it.z0 + 2 * ( warp % ZP ); // this warp's output slices zA, zA+1
    if ( zA > N - 3 )
       return;
-   const int    xc       = it.x0 - 1 + lane; // this lane's column
+   const int x0w = it.x0 + XOUT * ( warp / ZP ); // first output column of this warp
+   if ( N - 1 - zA - x0w < it.ya )
+      return; // the warp's columns have no interior point in the item's rows
+   const int    xc       = x0w - 1 + lane; // this lane's column
    const size_t cellBase = (size_t) cell * lv.cellSize;
 
    const double* w    = c_W[sa.constBase + cell];
@@ -116,23 +129,27 @@ __global__ void __maxnreg__( REGS ) hb_shuffle_kernel( const HbLevelView lv, con
    const u64 srcB  = (u64) ( sa.srcArena + ( ( sa.sync & 2 ) ? 0 : cellBase ) );
    const u64 dstB  = (u64) ( a.dst + cellBase );
    const u64 exB   = EX ? (u64) ( sa.extraArena + cellBase ) : 0ull;
-   const int ya    = it.ya, nOut = it.nOut;
+   const int ya    = it.ya, nOut = it.nOut; // CTA-uniform trip count: keeps the shuffles in provably convergent code
    const int rowIn = row_base( N, ya - 1, zA - 1 ) + xc; // slice zA-1, row ya-1
    u64       P0    = srcB + 8ull * (u64) rowIn;
    u64       P1    = srcB + 8ull * (u64) ( row_base( N, ya - 1, zA ) + xc );
    u64       P2    = srcB + 8ull * (u64) ( row_base( N, ya - 1, zA + 1 ) + xc );
    u64       P3    = srcB + 8ull * (u64) ( row_base( N, ya - 1, zA + 2 ) + xc );
    int       ld    = ( N + 2 - zA ) - ( ya - 1 ); // pitch of slice zA-1 at the row the P's point to
-   const int oi0 = row_base( N, ya, zA ) + xc, oi1 = row_base( N, ya, zA + 1 ) + xc;
+   // CHAIN2 (plain apply): the partial sums travel lane x-1 -> x -> x+1 as accumulator seeds (no DADD at all), so the output of
+   // column x ends up in lane x+1; the fused modes need the centre value / operand of the output column and keep it in lane x.
+   constexpr bool CHAIN2 = ( MODE == HB_APPLY_REPLACE );
+   const int      xo     = CHAIN2 ? xc - 1 : xc; // output column of this lane
+   const int oi0 = row_base( N, ya, zA ) + xo, oi1 = row_base( N, ya, zA + 1 ) + xo;
    u64       O0 = dstB + 8ull * (u64) oi0, O1 = dstB + 8ull * (u64) oi1; // output row of the block's first iteration
    u64       E0 = exB + 8ull * (u64) oi0, E1 = exB + 8ull * (u64) oi1;   // next row of the fused operand to load
    int       so = ( N + 1 - zA ) - ya;                                   // pitch of slice zA at the row O0 / E0 point to
    int       se = so;
    const long long auxOff = ( MODE == HB_CHEB_STEP ) ? (long long) ( (u64) a.aux - (u64) a.dst ) : 0ll;
 
-   const bool laneOut = ( lane >= 1 ) && ( lane <= XOUT );
-   const int  yMax0   = laneOut ? min( ya + nOut - 1, min( N - 2 - zA, N - 1 - zA - xc ) ) : -1;
-   const int  yMax1   = ( laneOut && zA + 1 <= N - 3 ) ? min( ya + nOut - 1, min( N - 3 - zA, N - 2 - zA - xc ) ) : -1;
+   const bool laneOut = CHAIN2 ? ( lane >= 2 ) : ( ( lane >= 1 ) && ( lane <= XOUT ) );
+   const int  yMax0   = laneOut ? min( ya + nOut - 1, min( N - 2 - zA, N - 1 - zA - xo ) ) : -1;
+   const int  yMax1   = ( laneOut && zA + 1 <= N - 3 ) ? min( ya + nOut - 1, min( N - 3 - zA, N - 2 - zA - xo ) ) : -1;
    int        r0 = ( sa.sync & 4 ) ? 0 : max( 0, yMax0 - ya + 1 ), r1 = ( sa.sync & 4 ) ? 0 : max( 0, yMax1 - ya + 1 ); // rows this lane still has to store in slice zA / zA+1
    // SOR: colour (x + 2y + 3z) mod 4 of the output point (same colouring as the generic kernel); k0 == 0 mod 4 <=> slice zA matches
    int k0 = ( MODE == HB_SOR ) ? ( xc + 2 * ya + 3 * zA - a.colour ) : 0;
@@ -231,41 +248,61 @@ __global__ void __maxnreg__( REGS ) hb_shuffle_kernel( const HbLevelView lv, con
             }
          }
 
-         // output (zA, y): below = slice 0, own = 1, above = 2
-         double c0 = w[D_C] * B1;
+         // left 4-tap partial sums of both outputs: evaluated for the lane to the right
+         double l0 = w[D_W] * B1;
+         l0        = fma( w[D_NW], N1, l0 );
+         l0        = fma( w[D_BNW], N0, l0 );
+         l0        = fma( w[D_TW], B2, l0 );
+         double l1 = w[D_W] * B2;
+         l1        = fma( w[D_NW], N2, l1 );
+         l1        = fma( w[D_BNW], N1, l1 );
+         l1        = fma( w[D_TW], B3, l1 );
+         // centre-column taps, seeded with the left neighbour's partial sum.  output (zA, y): below = slice 0, own = 1, above = 2
+         double c0 = __shfl_up_sync( 0xffffffffu, l0, 1 );
+         c0        = fma( w[D_C], B1, c0 );
          c0        = fma( w[D_N], N1, c0 );
          c0        = fma( w[D_S], A1, c0 );
          c0        = fma( w[D_BC], B0, c0 );
          c0        = fma( w[D_BN], N0, c0 );
          c0        = fma( w[D_TC], B2, c0 );
          c0        = fma( w[D_TS], A2, c0 );
-         double l0 = w[D_W] * B1;
-         l0        = fma( w[D_NW], N1, l0 );
-         l0        = fma( w[D_BNW], N0, l0 );
-         l0        = fma( w[D_TW], B2, l0 );
-         double r0v = w[D_E] * B1;
-         r0v        = fma( w[D_SE], A1, r0v );
-         r0v        = fma( w[D_BE], B0, r0v );
-         r0v        = fma( w[D_TSE], A2, r0v );
          // output (zA+1, y): below = slice 1, own = 2, above = 3
-         double c1 = w[D_C] * B2;
+         double c1 = __shfl_up_sync( 0xffffffffu, l1, 1 );
+         c1        = fma( w[D_C], B2, c1 );
          c1        = fma( w[D_N], N2, c1 );
          c1        = fma( w[D_S], A2, c1 );
          c1        = fma( w[D_BC], B1, c1 );
          c1        = fma( w[D_BN], N1, c1 );
          c1        = fma( w[D_TC], B3, c1 );
          c1        = fma( w[D_TS], A3, c1 );
-         double l1 = w[D_W] * B2;
-         l1        = fma( w[D_NW], N2, l1 );
-         l1        = fma( w[D_BNW], N1, l1 );
-         l1        = fma( w[D_TW], B3, l1 );
-         double r1v = w[D_E] * B2;
-         r1v        = fma( w[D_SE], A2, r1v );
-         r1v        = fma( w[D_BE], B1, r1v );
-         r1v        = fma( w[D_TSE], A3, r1v );
-
-         const double Ax0 = c0 + __shfl_up_sync( 0xffffffffu, l0, 1 ) + __shfl_down_sync( 0xffffffffu, r0v, 1 );
-         const double Ax1 = c1 + __shfl_up_sync( 0xffffffffu, l1, 1 ) + __shfl_down_sync( 0xffffffffu, r1v, 1 );
+         double Ax0, Ax1;
+         if ( CHAIN2 )
+         {
+            // right taps: this lane's values are the right neighbours of column x-1, whose sum so far arrives from lane x-1
+            Ax0 = __shfl_up_sync( 0xffffffffu, c0, 1 );
+            Ax0 = fma( w[D_E], B1, Ax0 );
+            Ax0 = fma( w[D_SE], A1, Ax0 );
+            Ax0 = fma( w[D_BE], B0, Ax0 );
+            Ax0 = fma( w[D_TSE], A2, Ax0 );
+            Ax1 = __shfl_up_sync( 0xffffffffu, c1, 1 );
+            Ax1 = fma( w[D_E], B2, Ax1 );
+            Ax1 = fma( w[D_SE], A2, Ax1 );
+            Ax1 = fma( w[D_BE], B1, Ax1 );
+            Ax1 = fma( w[D_TSE], A3, Ax1 );
+         }
+         else
+         {
+            double r0v = w[D_E] * B1;
+            r0v        = fma( w[D_SE], A1, r0v );
+            r0v        = fma( w[D_BE], B0, r0v );
+            r0v        = fma( w[D_TSE], A2, r0v );
+            double r1v = w[D_E] * B2;
+            r1v        = fma( w[D_SE], A2, r1v );
+            r1v        = fma( w[D_BE], B1, r1v );
+            r1v        = fma( w[D_TSE], A3, r1v );
+            Ax0        = c0 + __shfl_down_sync( 0xffffffffu, r0v, 1 );
+            Ax1        = c1 + __shfl_down_sync( 0xffffffffu, r1v, 1 );
+         }
 
          bool s0 = u < r0, s1 = u < r1;
          if ( MODE == HB_SOR )
@@ -313,7 +350,7 @@ __global__ void __maxnreg__( REGS ) hb_shuffle_kernel( const HbLevelView lv, con
    };
    int left = nOut; // output rows still to produce
    // optional CTA-wide pacing: the warps of a CTA share input slices pairwise, keeping them on the same rows keeps those in L1
-   const int nSync = ( sa.sync & 1 ) ? 32 * min( PAIRS, ( N - 3 - it.z0 ) / 2 + 1 ) : 0;
+   const int nSync = ( ( sa.sync & 1 ) && XCH == 1 ) ? 32 * min( PAIRS, ( N - 3 - it.z0 ) / 2 + 1 ) : 0;
    while ( nLoad >= DEPTH )
    {
       if ( nSync )
@@ -432,11 +469,11 @@ void hb_launch_shuffle_stencil( int mode, const HbLevelView& lv, const HbStencil
 void hb_shuffle_build_items( int N, std::vector< HbItem >& items, int ys, int order )
 {
    // ys + 2 input rows per item: a multiple of DEPTH_DEFAULT keeps the last unrolled block full
-   const int ZBh = 2 * PAIRS, YS = ys > 0 ? ys : 48;
+   const int ZBh = 2 * ZP, YS = ys > 0 ? ys : 48;
    items.clear();
    std::vector< long long > work;
    for ( int z0 = 1; z0 <= N - 3; z0 += ZBh )
-      for ( int x0 = 1; x0 <= N - 2 - z0; x0 += XOUT )
+      for ( int x0 = 1; x0 <= N - 2 - z0; x0 += XOUT * XCH )
       {
          const int yMax = N - 1 - z0 - x0; // last row with a valid point at column x0 in slice z0
          for ( int ya = 1; ya <= yMax; ya += YS )
@@ -451,8 +488,9 @@ void hb_shuffle_build_items( int N, std::vector< HbItem >& items, int ys, int or
       }
    // largest items first (work ~ rows x active warps): the tail of the grid is made of the small items at the diagonal
    auto cost = [N]( const HbItem& it ) {
-      const int nz = std::min( 2 * PAIRS, N - 2 - it.z0 );
-      return (long long) ( it.nOut + 2 + DEPTH_DEFAULT ) * ( ( nz + 1 ) / 2 );
+      const int nz = std::min( 2 * ZP, N - 2 - it.z0 );
+      const int nx = std::min( XCH, ( N - 2 - it.z0 - it.x0 - it.ya ) / XOUT + 1 );
+      return (long long) ( it.nOut + 2 + DEPTH_DEFAULT ) * ( ( nz + 1 ) / 2 ) * nx;
    };
    if ( order == 2 ) // x fastest: consecutive CTAs read neighbouring column chunks of the same rows
       std::stable_sort( items.begin(), items.end(), []( const HbItem& a, const HbItem& b ) {

@@ -150,3 +150,109 @@ def test_interior_kernels_agree(cuda_lib, name, L):
         assert np.array_equal(c[k], b[k]), (k, np.abs(c[k] - b[k]).max())
         # shuffle kernel: the 15 taps are summed in three column groups -> equal up to rounding
         assert np.abs(a[k] - b[k]).max() <= 1e-13 * np.abs(b[k]).max(), (k, np.abs(a[k] - b[k]).max())
+
+
+@pytest.mark.parametrize("name,L", [("cube_6el", 5), ("regular_octahedron_8el", 6)])
+def test_sor_shuffle_kernel_matches_generic(cuda_lib, name, L):
+    """the four interior colours of smooth_sor through the shuffle kernel (sm_100a hot path) against the generic tile kernel:
+    same colouring and phase order, sums associated differently -> equal up to rounding; forward and backward sweeps"""
+    v, c = meshes.golden(name)
+    st = api.PrimitiveStorage(v, c, lib=cuda_lib)
+    st.setMeshBoundaryFlagsOnBoundary(1, 0, True)
+    A = api.P1ConstantLaplaceOperator(st, L, L)
+    x, b = api.P1Function("x", st, L, L), api.P1Function("b", st, L, L)
+    fx = lambda X, Y, Z: np.sin(5 * X) * np.cos(3 * Y) + Z
+    fb = lambda X, Y, Z: np.cos(X + 2 * Y) * Z
+
+    def run(shuffle):
+        cuda_lib.dll.hb_set_tuning(b"sor_shuffle", shuffle)
+        x.interpolate(fx, L, All)
+        b.interpolate(fb, L, All)
+        for _ in range(2):
+            A.smooth_sor(x, b, 1.0, L, pc.SMOOTH)
+            A.smooth_sor(x, b, 1.2, L, pc.SMOOTH, backwards=True)
+        return x.download(L)
+
+    try:
+        a, g = run(1), run(0)
+    finally:
+        cuda_lib.dll.hb_set_tuning(b"sor_shuffle", 1)
+    assert np.abs(a - g).max() <= 1e-12 * np.abs(g).max(), np.abs(a - g).max()
+
+
+def test_bench_size_properties(cuda_lib):
+    """BASELINE config[1] size, cube_6el level 8 (16 974 593 DoFs): A*linear = 0 (P1LaplaceOperator3DTest.cpp bound), symmetry
+    <Ax,y> = <x,Ay>, one Jacobi sweep == x + w D^-1 (b - A x) assembled from apply/diagonal, SOR reduces the residual, and
+    every copy of an interface DoF holds the same value afterwards."""
+    L = 8
+    v, c = meshes.golden("cube_6el")
+    st = api.PrimitiveStorage(v, c, lib=cuda_lib)
+    st.setMeshBoundaryFlagsOnBoundary(1, 0, True)
+    A = api.P1ConstantLaplaceOperator(st, L, L)
+    u, r, w, t, d = (api.P1Function(n, st, L, L) for n in "urwtd")
+    u.interpolate(lambda x, y, z: 2 * x + 3 * y - 7 * z + 1, L, All)
+    A.apply(u, r, L, Inner)
+    n = st.num_global_dofs(L)
+    assert n == 16974593
+    assert np.sqrt(r.dotGlobal(r, L, Inner) / n) < 2.8e-13
+    u.interpolate(lambda x, y, z: np.sin(3 * x) * y + z * z, L, Inner)
+    u.interpolate(0.0, L, DirichletBoundary)
+    w.interpolate(lambda x, y, z: np.cos(2 * y) * x - z, L, Inner)
+    w.interpolate(0.0, L, DirichletBoundary)
+    A.apply(u, r, L, Inner)
+    A.apply(w, t, L, Inner)
+    a, b = r.dotGlobal(w, L, Inner), t.dotGlobal(u, L, Inner)
+    assert abs(a - b) < 1e-11 * abs(a), (a, b)
+    # Jacobi from its parts: t = u + 0.66 * D^-1 (w - A u) on inner DoFs (r = A u from above)
+    A.smooth_jac(t, w, u, 0.66, L, Inner)
+    A.diagonal(d, L, inverse=True)
+    r.assign([1.0, -1.0], [w, r], L, Inner)         # r = w - A u
+    r.multElementwise([r, d], L, Inner)             # r = D^-1 (w - A u)
+    r.assign([1.0, 0.66], [u, r], L, Inner)         # r = u + 0.66 r
+    r.add([-1.0], [t], L, Inner)
+    assert r.getMaxDoFMagnitude(L, Inner) < 1e-12 * max(1.0, t.getMaxDoFMagnitude(L, Inner))
+    # SOR sweeps reduce the residual of A x = 0 with Dirichlet data and keep the copies of interface DoFs consistent
+    u.interpolate(lambda x, y, z: np.sin(x) * np.sinh(y) + z, L, DirichletBoundary)
+    w.interpolate(0.0, L, All)
+    A.residual(u, w, r, L, Inner)
+    r0 = np.sqrt(r.dotGlobal(r, L, Inner))
+    for _ in range(3):
+        A.smooth_sor(u, w, 1.0, L, pc.SMOOTH)
+    A.residual(u, w, r, L, Inner)
+    r1 = np.sqrt(r.dotGlobal(r, L, Inner))
+    assert r1 < 0.5 * r0, (r0, r1)
+    arr = u.download(L)
+    m = st.cell_array_size(L)
+    N = 2 ** L
+    # macro-cells 0 and 1 of cube_6el share the face (1,3,4): compare through the coordinates of the micro vertices
+    xyz = st.micro_coordinates(L).reshape(st.num_local_cells, m, 3)
+    key = lambda p: np.round(p * N).astype(np.int64) @ np.array([1, N + 1, (N + 1) ** 2])
+    k0, k1 = key(xyz[0]), key(xyz[1])
+    common, i0, i1 = np.intersect1d(k0, k1, return_indices=True)
+    assert len(common) == (N + 1) * (N + 2) // 2
+    assert np.array_equal(arr[:m][i0], arr[m:2 * m][i1])
+
+
+@pytest.mark.parametrize("name,L", [("cube_6el", 2), ("cube_6el", 4), ("regular_octahedron_8el", 3), ("pyramid_tilted_4el", 1)])
+def test_sor_single_launch_matches_multi_launch(cuda_lib, name, L):
+    """coarse levels: the whole SOR sweep in one single-CTA launch (hb_sor_small_kernel) == the 16-launch path, bit for bit"""
+    v, c = meshes.golden(name)
+    st = api.PrimitiveStorage(v, c, lib=cuda_lib)
+    st.setMeshBoundaryFlagsOnBoundary(1, 0, True)
+    A = api.P1ConstantLaplaceOperator(st, L, L)
+    x, b = api.P1Function("x", st, L, L), api.P1Function("b", st, L, L)
+
+    def run(small):
+        cuda_lib.dll.hb_set_tuning(b"sor_small", small)
+        x.interpolate(lambda X, Y, Z: np.sin(5 * X) * np.cos(3 * Y) + Z, L, All)
+        b.interpolate(lambda X, Y, Z: np.cos(X + 2 * Y) * Z, L, All)
+        for _ in range(2):
+            A.smooth_sor(x, b, 1.0, L, pc.SMOOTH)
+            A.smooth_sor(x, b, 1.3, L, pc.SMOOTH, backwards=True)
+        return x.download(L)
+
+    try:
+        a, g = run(1), run(0)
+    finally:
+        cuda_lib.dll.hb_set_tuning(b"sor_small", 1)
+    assert np.array_equal(a, g), np.abs(a - g).max()
