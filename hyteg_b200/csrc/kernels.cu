@@ -14,6 +14,8 @@
 
 #ifdef HB_EMUL
 dim3 threadIdx, blockIdx, blockDim, gridDim;
+#else
+#include <cooperative_groups.h>
 #endif
 
 #define HB_WPB 8 // warps (z-slices) per interior block
@@ -326,6 +328,87 @@ __global__ void __launch_bounds__( 1024 ) hb_sor_small_kernel( const HbLevelView
    }
 }
 #endif
+
+// All interface phases of one SOR sweep (macro vertices, edges in 2 colours, faces in 3 colours; each evaluated into scratch,
+// then committed) in ONE cooperative launch: persistent CTAs walk the (macro-cell, chunk) blocks of every phase and meet at a
+// grid barrier between the passes, instead of 12 launches.  Same arithmetic as hb_interface_kernel< HB_SOR > + hb_commit_kernel.
+#ifndef HB_EMUL
+__device__ __forceinline__ void hb_commit_block( const HbLevelView& lv, const HbStencilArgs& a, int blk )
+{
+   const int cell = blk / lv.nChunks;
+   if ( cell >= lv.nCells )
+      return;
+   const HbBndChunk  ch  = lv.chunks[blk - cell * lv.nChunks];
+   const HbCellInfo* ci  = lv.cells + cell;
+   const HbRegion    reg = ci->region[ch.mask];
+   if ( !( reg.owner & 2 ) || !( ( a.selMask >> reg.bflag ) & 1 ) || !( ( a.dimSel >> reg.dim ) & 1 ) )
+      return;
+   if ( (int) threadIdx.x >= ch.count )
+      return;
+   const int        i = ch.first + threadIdx.x;
+   const HbBndPoint p = lv.bnd[i];
+   if ( a.bndColour >= 0 && hb_interface_colour( *ci, lv.N, p.x, p.y, p.z ) != a.bndColour )
+      return;
+   const double val = a.scratch[(size_t) cell * lv.nBnd + i];
+   for ( int e = ci->rcBegin[ch.mask]; e < ci->rcBegin[ch.mask + 1]; e++ )
+   {
+      const HbRegionCopy rc = lv.regionCopies[e];
+      if ( rc.slot < lv.nCells )
+         a.dst[(size_t) rc.slot * lv.cellSize + (size_t) hb_copy_index( lv.N, rc, p.x, p.y, p.z )] = val;
+   }
+}
+
+__global__ void __launch_bounds__( HB_BLOCK, 4 ) hb_sor_interface_coop_kernel( const HbLevelView lv, HbStencilArgs a, const int backwards )
+{
+   cooperative_groups::grid_group grid = cooperative_groups::this_grid();
+   const int nBlk = lv.nCells * lv.nChunks;
+   a.toScratch    = 1;
+   for ( int ph = 0; ph < 6; ph++ )
+   {
+      const int k   = backwards ? 5 - ph : ph;          // phases 0: vertices | 1,2: edges | 3,4,5: faces
+      const int dim = k == 0 ? 0 : ( k <= 2 ? 1 : 2 );
+      a.dimSel      = 1 << dim;
+      a.bndColour   = k == 0 ? 0 : ( k <= 2 ? k - 1 : k - 3 );
+      for ( int blk = blockIdx.x; blk < nBlk; blk += gridDim.x )
+         hb_boundary_block< HB_SOR >( lv, a, blk );
+      grid.sync();
+      for ( int blk = blockIdx.x; blk < nBlk; blk += gridDim.x )
+         hb_commit_block( lv, a, blk );
+      grid.sync();
+   }
+}
+#endif
+
+bool hb_launch_sor_interface_coop( const HbLevelView& lv, const HbStencilArgs& a, int backwards, cudaStream_t st )
+{
+#ifdef HB_EMUL
+   return false;
+#else
+   static int perSm = -1, nSm = 0, coop = 0;
+   if ( perSm < 0 )
+   {
+      int dev = 0;
+      cudaGetDevice( &dev );
+      cudaDeviceGetAttribute( &nSm, cudaDevAttrMultiProcessorCount, dev );
+      cudaDeviceGetAttribute( &coop, cudaDevAttrCooperativeLaunch, dev );
+      if ( cudaOccupancyMaxActiveBlocksPerMultiprocessor( &perSm, hb_sor_interface_coop_kernel, HB_BLOCK, 0 ) != cudaSuccess )
+         perSm = 0;
+   }
+   if ( !coop || perSm < 1 )
+      return false;
+   const int nBlk = lv.nCells * lv.nChunks;
+   int       grid = nSm * perSm;
+   if ( grid > nBlk )
+      grid = nBlk;
+   if ( grid < 1 )
+      return true;
+   HbLevelView   lvc = lv;
+   HbStencilArgs ac  = a;
+   int           bw  = backwards;
+   void*         args[] = { &lvc, &ac, &bw };
+   return cudaLaunchCooperativeKernel( (void*) hb_sor_interface_coop_kernel, dim3( grid ), dim3( HB_BLOCK ), args, 0, st ) == cudaSuccess;
+#endif
+}
 
 bool hb_launch_sor_small( const HbLevelView& lv, const HbStencilArgs& a, int backwards, cudaStream_t st )
 {
@@ -644,38 +727,60 @@ __global__ void hb_restrict_kernel( const HbLevelView coarse, const HbLevelView 
    const int    N      = coarse.N;
    for ( size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride )
    {
-      const int cell  = (int) ( i / (size_t) coarse.cellSize );
-      const int local = (int) ( i - (size_t) cell * coarse.cellSize );
+      const int         cell  = (int) ( i / (size_t) coarse.cellSize );
+      const int         local = (int) ( i - (size_t) cell * coarse.cellSize );
+      const HbBndPoint  q     = coarse.xyz[local];
+      const int         x = q.x, y = q.y, z = q.z;
+      const int         m  = q.mask;
+      const HbCellInfo* ci = coarse.cells + cell;
+      if ( !( bc.type[ci->region[m].bflag] & flag ) )
+         continue;
+      double acc = 0.0;
+      if ( m == 0 )
       {
-         const HbBndPoint q = coarse.xyz[local];
-         const int        x = q.x, y = q.y, z = q.z;
-         const int m = hb_mask( N, x, y, z );
-         const HbCellInfo ci = coarse.cells[cell];
-         if ( !( bc.type[ci.region[m].bflag] & flag ) )
-            continue;
-         double acc = 0.0;
-         if ( m == 0 )
-            acc = hb_restrict_partial( fine, fsrc[cell], cell, x, y, z );
-         else
-         {
-            const int b[4] = { N - x - y - z, x, y, z };
-            int       supp = 0;
-            for ( int j = 0; j < 4; j++ )
-               supp |= ( b[j] != 0 ) << j;
-            for ( int e = ci.copyBegin; e < ci.copyEnd; e++ )
-            {
-               const HbCopy cp = coarse.copies[e];
-               if ( supp & ~cp.sharedMask )
-                  continue;
-               int bp[4] = { 0, 0, 0, 0 };
-               for ( int j = 0; j < 4; j++ )
-                  if ( ( supp >> j ) & 1 )
-                     bp[cp.vmap[j]] = b[j];
-               acc += hb_restrict_partial( fine, fsrc[cp.slot], cp.slot, bp[1], bp[2], bp[3] );
-            }
-         }
-         cdst[i] = acc;
+         // interior coarse point: the fine point 2(x,y,z) and its 14 neighbours are interior points of the same macro-cell
+         // (multiplicity 1), so hb_restrict_partial reduces to f[c] + 0.5 * sum f[c + d] -- same order, no divisions
+         const double* __restrict__ f = fsrc[cell];
+         const int Nf = fine.N, xf = 2 * x, yf = 2 * y, zf = 2 * z;
+         const int ws   = Nf + 1 - zf;
+         const int i0   = hb_index( Nf, xf, yf, zf );
+         const int szUp = ( ws * ( ws + 1 ) ) / 2, szDn = ( ( ws + 1 ) * ( ws + 2 ) ) / 2;
+         const int dN = ws - yf, dS = -( ws - yf + 1 ), dT = szUp - yf, dTS = szUp - ws, dB = yf - szDn, dBN = ws + 1 - szDn;
+         acc = f[i0];
+         acc += 0.5 * f[i0 - 1];        // W
+         acc += 0.5 * f[i0 + 1];        // E
+         acc += 0.5 * f[i0 + dN];       // N
+         acc += 0.5 * f[i0 + dS];       // S
+         acc += 0.5 * f[i0 + dN - 1];   // NW
+         acc += 0.5 * f[i0 + dS + 1];   // SE
+         acc += 0.5 * f[i0 + dT];       // TC
+         acc += 0.5 * f[i0 + dT - 1];   // TW
+         acc += 0.5 * f[i0 + dTS];      // TS
+         acc += 0.5 * f[i0 + dTS + 1];  // TSE
+         acc += 0.5 * f[i0 + dB];       // BC
+         acc += 0.5 * f[i0 + dBN];      // BN
+         acc += 0.5 * f[i0 + dB + 1];   // BE
+         acc += 0.5 * f[i0 + dBN - 1];  // BNW
       }
+      else
+      {
+         const int b[4] = { N - x - y - z, x, y, z };
+         int       supp = 0;
+         for ( int j = 0; j < 4; j++ )
+            supp |= ( b[j] != 0 ) << j;
+         for ( int e = ci->copyBegin; e < ci->copyEnd; e++ )
+         {
+            const HbCopy cp = coarse.copies[e];
+            if ( supp & ~cp.sharedMask )
+               continue;
+            int bp[4] = { 0, 0, 0, 0 };
+            for ( int j = 0; j < 4; j++ )
+               if ( ( supp >> j ) & 1 )
+                  bp[cp.vmap[j]] = b[j];
+            acc += hb_restrict_partial( fine, fsrc[cp.slot], cp.slot, bp[1], bp[2], bp[3] );
+         }
+      }
+      cdst[i] = acc;
    }
 }
 

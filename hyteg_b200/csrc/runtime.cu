@@ -308,7 +308,10 @@ int hb_set_allreduce( hb_allreduce_fn fn, void* ctx )
 
 int hb_set_tuning( const char* key, int value )
 {
-   hb::g_tuning[key] = value;
+   if ( value == -2147483647 - 1 ) // INT_MIN: back to the built-in default
+      hb::g_tuning.erase( key );
+   else
+      hb::g_tuning[key] = value;
    return 0;
 }
 

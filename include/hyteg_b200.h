@@ -71,7 +71,8 @@ typedef int ( *hb_exchange_fn )( void* ctx, int n_peers, const int* peers, doubl
 int hb_set_exchange( hb_exchange_fn fn, void* ctx );
 /* number of ghost exchanges done so far and doubles sent by this rank (all functions, all levels) */
 int hb_exchange_stats( long long* calls, long long* doubles_sent );
-/* tuning knobs for kernel experiments: "tile_rows" */
+/* tuning knobs for kernel experiments and A/B tests ("interior", "overlap", "shuffle_depth", "sor_shuffle", "sor_small",
+ * "sor_coop", "apply_parts", ...); value INT_MIN restores the built-in default */
 int hb_set_tuning( const char* key, int value );
 
 /* ---- PrimitiveStorage  (src/hyteg/primitivestorage/SetupPrimitiveStorage.hpp, PrimitiveStorage.hpp) */

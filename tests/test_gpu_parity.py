@@ -176,7 +176,7 @@ def test_sor_shuffle_kernel_matches_generic(cuda_lib, name, L):
     try:
         a, g = run(1), run(0)
     finally:
-        cuda_lib.dll.hb_set_tuning(b"sor_shuffle", 1)
+        cuda_lib.dll.hb_set_tuning(b"sor_shuffle", -2147483648)
     assert np.abs(a - g).max() <= 1e-12 * np.abs(g).max(), np.abs(a - g).max()
 
 
@@ -254,5 +254,30 @@ def test_sor_single_launch_matches_multi_launch(cuda_lib, name, L):
     try:
         a, g = run(1), run(0)
     finally:
-        cuda_lib.dll.hb_set_tuning(b"sor_small", 1)
+        cuda_lib.dll.hb_set_tuning(b"sor_small", -2147483648)
+    assert np.array_equal(a, g), np.abs(a - g).max()
+
+
+@pytest.mark.parametrize("name,L", [("cube_6el", 5), ("regular_octahedron_8el", 5), ("three_tets_with_two_joint_faces", 6)])
+def test_sor_cooperative_interface_matches_multi_launch(cuda_lib, name, L):
+    """the six interface phases of an SOR sweep in one cooperative launch (grid barriers) == the 12-launch path, bit for bit"""
+    v, c = meshes.golden(name)
+    st = api.PrimitiveStorage(v, c, lib=cuda_lib)
+    st.setMeshBoundaryFlagsOnBoundary(1, 0, True)
+    A = api.P1ConstantLaplaceOperator(st, L, L)
+    x, b = api.P1Function("x", st, L, L), api.P1Function("b", st, L, L)
+
+    def run(coop):
+        cuda_lib.dll.hb_set_tuning(b"sor_coop", coop)
+        x.interpolate(lambda X, Y, Z: np.sin(5 * X) * np.cos(3 * Y) + Z, L, All)
+        b.interpolate(lambda X, Y, Z: np.cos(X + 2 * Y) * Z, L, All)
+        for _ in range(2):
+            A.smooth_sor(x, b, 1.0, L, pc.SMOOTH)
+            A.smooth_sor(x, b, 1.3, L, pc.SMOOTH, backwards=True)
+        return x.download(L)
+
+    try:
+        a, g = run(1), run(0)
+    finally:
+        cuda_lib.dll.hb_set_tuning(b"sor_coop", -2147483648)
     assert np.array_equal(a, g), np.abs(a - g).max()

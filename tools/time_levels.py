@@ -1,0 +1,32 @@
+"""Per-level times of the building blocks of the V-cycle (CUDA events): SOR sweep, residual, restrict, prolongate."""
+import os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+import hyteg_b200 as hb
+from hyteg_b200 import api, meshes
+lib = hb.get_lib(); lib.check(lib.dll.hb_device_init(0))
+s = torch.cuda.current_stream(); lib.dll.hb_set_stream(s.cuda_stream)
+v, c = meshes.cube_6el()
+LMAX = 8
+st = api.PrimitiveStorage(v, c); st.setMeshBoundaryFlagsOnBoundary(1, 0, True)
+A = api.P1ConstantLaplaceOperator(st, 0, LMAX)
+x, b, r = (api.P1Function(n, st, 0, LMAX) for n in "xbr")
+R, P = api.P1toP1LinearRestriction(), api.P1toP1LinearProlongation()
+def t(fn, n=20):
+    for _ in range(3): fn()
+    torch.cuda.synchronize()
+    a, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record(s)
+    for _ in range(n): fn()
+    e.record(s); torch.cuda.synchronize()
+    return a.elapsed_time(e) / n * 1e3
+tot = 0.0
+for L in range(1, LMAX + 1):
+    sor = t(lambda: A.smooth_sor(x, b, 1.0, L, hb.SMOOTH_FLAG))
+    res = t(lambda: A.residual(x, b, r, L, hb.Inner))
+    rs = t(lambda: R.restrict(r, L, hb.SMOOTH_FLAG))
+    pr = t(lambda: P.prolongateAndAdd(x, L - 1, hb.SMOOTH_FLAG))
+    lvl = 6 * sor + res + rs + pr
+    tot += lvl
+    print(f"L{L}: sor {sor:8.1f} us  residual {res:7.1f}  restrict {rs:7.1f}  prolongateAndAdd {pr:7.1f}  | V(3,3) share {lvl:8.1f} us")
+print(f"sum over levels {tot/1e3:.2f} ms (plus CG on level 0)")
