@@ -35,3 +35,4 @@ void hb_launch_unpack( double* arena, const long long* off, long long n, const d
 bool hb_launch_sor_small( const HbLevelView& lv, const HbStencilArgs& a, int backwards, cudaStream_t st );
 // the six interface phases (+ commits) of an SOR sweep in one cooperative launch; false if unavailable
 bool hb_launch_sor_interface_coop( const HbLevelView& lv, const HbStencilArgs& a, int backwards, cudaStream_t st );
+extern int hb_use_desc; // 1: interface kernel reads per-block descriptors, 0: walks the topology tables (default)

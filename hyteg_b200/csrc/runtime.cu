@@ -86,6 +86,7 @@ void hb_storage::uploadTopologyTables()
    dRegionCopies.upload( view.regionCopies );
    for ( auto& kv : levels )
    {
+      buildChunkDescs( *kv.second );
       kv.second->view.cells  = dCells.ptr;
       kv.second->view.copies = dCopies.ptr;
       kv.second->view.regionCopies = dRegionCopies.ptr;
@@ -93,6 +94,34 @@ void hb_storage::uploadTopologyTables()
    }
    tablesDirty = false;
    g_constOwner = nullptr; // macro-cell flags may have changed
+}
+
+void hb_storage::buildChunkDescs( hb::LevelTables& lt )
+{
+   static_assert( sizeof( HbChunkDesc ) == 160, "HbChunkDesc layout" );
+   std::vector< HbChunkDesc > d( (size_t) view.nLocal * lt.hChunks.size() );
+   for ( int c = 0; c < view.nLocal; c++ )
+      for ( size_t k = 0; k < lt.hChunks.size(); k++ )
+      {
+         const HbBndChunk& ch = lt.hChunks[k];
+         const HbCellInfo& ci = view.cells[c];
+         HbChunkDesc&      o  = d[(size_t) c * lt.hChunks.size() + k];
+         std::memset( &o, 0, sizeof( o ) );
+         o.first   = ch.first;
+         o.count   = ch.count;
+         o.mask    = (uint8_t) ch.mask;
+         o.bflag   = ci.region[ch.mask].bflag;
+         o.owner   = ci.region[ch.mask].owner;
+         o.dim     = ci.region[ch.mask].dim;
+         o.nCopies = ci.rcBegin[ch.mask + 1] - ci.rcBegin[ch.mask];
+         for ( int j = 0; j < 4; j++ )
+            o.gv[j] = ci.gv[j];
+         if ( o.nCopies <= HB_DESC_MAXC )
+            for ( int e = 0; e < o.nCopies; e++ )
+               o.rc[e] = view.regionCopies[ci.rcBegin[ch.mask] + e];
+      }
+   lt.descs.upload( d );
+   lt.view.descs = lt.descs.ptr;
 }
 
 hb::LevelTables& hb_storage::level( int L )
@@ -154,6 +183,7 @@ hb::LevelTables& hb_storage::level( int L )
       i = j;
    }
    lt->chunks.upload( chunks );
+   lt->hChunks = chunks;
    lt->bnd.upload( bnd );
    lt->xyz.upload( lt->hXyz );
    lt->mask.upload( mask );
@@ -184,6 +214,7 @@ hb::LevelTables& hb_storage::level( int L )
    v.regionCopies = dRegionCopies.ptr;
    v.chunks       = lt->chunks.ptr;
    v.nChunks      = (int) chunks.size();
+   buildChunkDescs( *lt );
    auto& ref      = *lt;
    levels[L]      = std::move( lt );
    return ref;
@@ -308,6 +339,8 @@ int hb_set_allreduce( hb_allreduce_fn fn, void* ctx )
 
 int hb_set_tuning( const char* key, int value )
 {
+   if ( std::string( key ) == "iface_desc" )
+      hb_use_desc = ( value == -2147483647 - 1 ) ? 0 : value;
    if ( value == -2147483647 - 1 ) // INT_MIN: back to the built-in default
       hb::g_tuning.erase( key );
    else

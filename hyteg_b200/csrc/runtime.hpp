@@ -63,6 +63,8 @@ struct LevelTables
    DeviceBuffer< uint8_t >    mask;
    DeviceBuffer< HbTile >     tiles;
    DeviceBuffer< HbBndChunk > chunks;
+   std::vector< HbBndChunk >  hChunks;
+   DeviceBuffer< HbChunkDesc > descs; // per (local macro-cell, chunk), rebuilt with the topology tables
    DeviceBuffer< HbItem >     items;   // work items of the TMA-streamed interior kernel
    DeviceBuffer< HbItem >     itemsShuffle; // work items of the centre-column + shuffle interior kernel
    DeviceBuffer< double >     scratch; // nCells*nBnd, interface staging (SOR)
@@ -97,7 +99,8 @@ struct hb_storage
    bool                                     tablesDirty = true;
 
    hb::LevelTables& level( int L );
-   hb::LevelTables::Exchange& exchange( int L ); // builds the level's exchange tables on first use
+   hb::LevelTables::Exchange& exchange( int L );
+   void             buildChunkDescs( hb::LevelTables& lt ); // builds the level's exchange tables on first use
    void             uploadTopologyTables();
    ~hb_storage();
 };

@@ -281,3 +281,48 @@ def test_sor_cooperative_interface_matches_multi_launch(cuda_lib, name, L):
     finally:
         cuda_lib.dll.hb_set_tuning(b"sor_coop", -2147483648)
     assert np.array_equal(a, g), np.abs(a - g).max()
+
+
+@pytest.mark.parametrize("name,L", [("cube_6el", 5), ("regular_octahedron_8el", 5), ("cube_24el", 5)])
+def test_interface_descriptor_kernel_matches_table_walk(cuda_lib, name, L):
+    """the interface kernel in descriptor form (shared-memory descriptors, both macro-cells' loads in flight) == the table-walking
+    form, bit for bit, for apply / apply-add / residual / Jacobi / Chebyshev step and the SOR phases"""
+    v, c = meshes.golden(name)
+    st = api.PrimitiveStorage(v, c, lib=cuda_lib)
+    st.setMeshBoundaryFlagsOnBoundary(1, 0, True)
+    A = api.P1ConstantLaplaceOperator(st, L, L)
+    n = st.num_local_cells * st.cell_array_size(L)
+    f = {k: api.P1Function(k, st, L, L) for k in ("src", "rhs", "dst", "x")}
+    fx = lambda X, Y, Z: np.sin(5 * X) * np.cos(3 * Y) + Z
+    fb = lambda X, Y, Z: np.cos(X + 2 * Y) * Z
+
+    def run(desc):
+        cuda_lib.dll.hb_set_tuning(b"iface_desc", desc)
+        cuda_lib.dll.hb_set_tuning(b"sor_coop", 0)
+        out = {}
+        f["src"].interpolate(fx, L, All)
+        f["rhs"].interpolate(fb, L, All)
+        f["x"].interpolate(fb, L, All)
+        A.apply(f["src"], f["dst"], L, All)
+        out["replace"] = f["dst"].download(L)
+        A.apply(f["src"], f["dst"], L, Inner, Add)
+        out["add"] = f["dst"].download(L)
+        A.residual(f["src"], f["rhs"], f["dst"], L, Inner)
+        out["residual"] = f["dst"].download(L)
+        A.smooth_jac(f["dst"], f["rhs"], f["src"], 0.66, L, All)
+        out["jacobi"] = f["dst"].download(L)
+        A.cheb_step(f["src"], f["dst"], f["x"], 0.37, L, All)
+        out["cheb_step"] = f["dst"].download(L)
+        out["cheb_step_x"] = f["x"].download(L)
+        A.smooth_sor(f["src"], f["rhs"], 1.0, L, pc.SMOOTH)
+        A.smooth_sor(f["src"], f["rhs"], 1.2, L, pc.SMOOTH, backwards=True)
+        out["sor"] = f["src"].download(L)
+        return out
+
+    try:
+        a, b = run(1), run(0)
+    finally:
+        cuda_lib.dll.hb_set_tuning(b"iface_desc", -2147483648)
+        cuda_lib.dll.hb_set_tuning(b"sor_coop", -2147483648)
+    for k in a:
+        assert np.array_equal(a[k], b[k]), (k, np.abs(a[k] - b[k]).max())
