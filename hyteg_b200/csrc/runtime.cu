@@ -486,16 +486,29 @@ int hb_storage_micro_coordinates( const hb_storage* cst, int level, double* xyz 
    const hb::Topology& t  = st->topo;
    const double        h  = 1.0 / (double) lt.view.N;
    size_t              o  = 0;
+   // Barycentric combination with the macro vertices taken in ascending GLOBAL id: every macro-cell that holds a copy of an
+   // interface point evaluates the same non-zero terms in the same order, so all copies get bit-identical coordinates (and
+   // interpolate( expression ) bit-identical values), whatever the local vertex order of the cell.
    for ( int l = 0; l < st->view.nLocal; l++ )
    {
       const int g = st->view.slotGlobal[l];
-      double    v[4][3];
-      for ( int j = 0; j < 4; j++ )
-         for ( int k = 0; k < 3; k++ )
-            v[j][k] = t.xyz[3 * t.cellV[g][j] + k];
+      int       ord[4] = { 0, 1, 2, 3 };
+      std::sort( ord, ord + 4, [&]( int a, int b ) { return t.cellV[g][a] < t.cellV[g][b]; } );
       for ( const HbBndPoint& p : lt.hXyz )
+      {
+         const int b[4] = { lt.view.N - p.x - p.y - p.z, p.x, p.y, p.z };
          for ( int k = 0; k < 3; k++ )
-            xyz[o++] = v[0][k] + h * ( p.x * ( v[1][k] - v[0][k] ) + p.y * ( v[2][k] - v[0][k] ) + p.z * ( v[3][k] - v[0][k] ) );
+         {
+            double acc = 0.0;
+            for ( int q = 0; q < 4; q++ )
+            {
+               const int j = ord[q];
+               if ( b[j] != 0 )
+                  acc += ( (double) b[j] * h ) * t.xyz[3 * t.cellV[g][j] + k];
+            }
+            xyz[o++] = acc;
+         }
+      }
    }
    return 0;
    HB_CATCH( 1 )

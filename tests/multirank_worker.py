@@ -29,14 +29,19 @@ def main():
     rank, world = dist.get_rank(), dist.get_world_size()
     lib = capi.Lib(os.path.join(ROOT, "tests", "emul", "libhyteg_b200_emul.so"))
     comm.init_callbacks(lib)
-    mesh = meshes.golden(mesh_name) if mesh_name != "cuboid" else meshes.cuboid(2, 1, 1)
+    if mesh_name == "cuboid":
+        mesh = meshes.cuboid(2, 1, 1)
+    elif mesh_name == "shell":  # BASELINE config[4] family: icosahedral spherical shell (60 macro-cells), many neighbours per rank
+        mesh = meshes.spherical_shell(2, 2)
+    else:
+        mesh = meshes.golden(mesh_name)
     L = 3
 
     # ---- apply / Jacobi / BLAS-1 / transfer against the oracle ---------------------------------------------------
     s = pc.Setup(lib, mesh, L - 1, L, rank, world)
     assert 0 < s.st.num_local_cells < len(mesh[1])
     npeers, nsend, nrecv = s.st.exchange_info(L)
-    assert npeers == world - 1 and nsend > 0 and nrecv > 0, (npeers, nsend, nrecv)
+    assert 1 <= npeers <= world - 1 and nsend > 0 and nrecv > 0, (npeers, nsend, nrecv)
     x, d0, b = s.rand(L, 1), s.rand(L, 2), s.rand(L, 3)
     src, dst, rhs = s.fn("src"), s.fn("dst"), s.fn("rhs")
     s.put(src, x, L)
