@@ -180,6 +180,9 @@ def main():
     lib.check(lib.dll.hb_set_stream(stream.cuda_stream))
 
     L = args.level
+    for kv in filter(None, os.environ.get("HB_TUNING", "").split(",")):  # A/B experiments: HB_TUNING="shuffle_depth=105,overlap=0"
+        k, val = kv.split("=")
+        lib.dll.hb_set_tuning(k.encode(), int(val))
     from hyteg_b200 import comm
     if world > 1:
         # weak scaling: a box of `world` unit cubes (6 macro-tets each), macro-cells partitioned in contiguous blocks so that
