@@ -257,25 +257,26 @@ def main():
     gmg_j = api.GeometricMultigridSolver(st, api.WeightedJacobiSmoother(st, 0, L, 0.66), api.CGSolver(st, 0, 0, 50, 1e-16, 1e-16), 0, L, 3, 3)
     ms_vj = timed(lambda: gmg_j.solve(A, x, b, L), max(args.steps // 10, 2), 2)
 
-    # end to end through the C-ABI with pinned HOST buffers: H2D src, apply, D2H dst every step.  Two requests are kept in
-    # flight on two streams (own functions and host buffers each), so the upload of one overlaps the download of the other
-    # (PCIe is full duplex); every step still moves its full input and output.
-    s2 = torch.cuda.Stream()
-    src2, dst2 = api.P1Function("src2", st, L, L), api.P1Function("dst2", st, L, L)
-    hout2 = torch.empty(n_arr, dtype=torch.float64).pin_memory()
-    lanes = [(stream, src, dst, hout), (s2, src2, dst2, hout2)]
-    n_e2e = max(args.steps // 5, 4)
+    # end to end through the C-ABI with pinned HOST buffers: H2D src, apply, D2H dst every step.  n_lanes requests are kept in
+    # flight on as many streams (own functions and host buffers each), so uploads overlap downloads (PCIe is full duplex);
+    # every step still moves its full input and output.
+    n_lanes = int(os.environ.get("HB_E2E_LANES", "2"))
+    lanes = [(stream, src, dst, hout)]
+    for k in range(1, n_lanes):
+        lanes.append((torch.cuda.Stream(), api.P1Function("src%d" % k, st, L, L), api.P1Function("dst%d" % k, st, L, L),
+                      torch.empty(n_arr, dtype=torch.float64).pin_memory()))
+    n_e2e = max(args.steps // 5, 4) // n_lanes * n_lanes + n_lanes
 
     def e2e_run(steps):
         for k in range(steps):
-            sk, fs, fd, ho = lanes[k % 2]
+            sk, fs, fd, ho = lanes[k % n_lanes]
             lib.check(lib.dll.hb_set_stream(sk.cuda_stream))
             lib.check(lib.dll.hb_p1function_upload_async(fs.h, L, C.cast(hp, dp)))
             A.apply(fs, fd, L, hb.Inner)
             lib.check(lib.dll.hb_p1function_download_async(fd.h, L, C.cast(ho.data_ptr(), dp)))
         lib.check(lib.dll.hb_set_stream(stream.cuda_stream))
 
-    e2e_run(4)
+    e2e_run(2 * n_lanes)
     barrier()
     t0 = time.perf_counter()
     e2e_run(n_e2e)
@@ -312,7 +313,7 @@ def main():
                          "sor_gdofs": gd(ms_sor), "sor_frac": BYTES_PER_DOF["sor"] * ndof_rank / (ms_sor * 1e-3) / 1e9 / peak,
                          "vcycle_3_3_gs_ms": ms_v, "vcycle_3_3_jacobi_ms": ms_vj, "ghost_exchanges_in_apply_region": ex0[0]},
                 "e2e": {"value": gd(ms_e2e), "unit": "GDoF/s", "h2d_bytes_per_step": 8 * n_arr, "d2h_bytes_per_step": 8 * n_arr,
-                        "note": "two requests in flight on two streams (upload of one overlaps download of the other)"},
+                        "note": "%d requests in flight on %d streams (uploads overlap downloads, PCIe full duplex)" % (n_lanes, n_lanes)},
                 "gpu_launches": 2 * args.steps + (2 * args.steps if world > 1 else 0), "clocks": clk.summary()}
         if not args.no_cpu_baseline and world == 1:
             line["cpu_baseline"] = cpu_reference_apply(min(L, 8), repeats=2)

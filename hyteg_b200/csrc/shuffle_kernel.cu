@@ -25,10 +25,11 @@
 
 namespace {
 
-// CTA shape: ZP z-slice pairs x XCH column chunks = PAIRS warps.  More column chunks per CTA make the CTA's DRAM accesses
+// CTA shape: ZP z-slice pairs x XCH column chunks = PAIRS warps.  Measured (level 8, us): 8x1 64.3, 4x1 62.0, 2x1 61.9, 4x2 68.3,
+// 2x4 73.9 -- small CTAs shorten the tail of the grid, column chunks in one CTA do not pay.  More column chunks per CTA make the CTA's DRAM accesses
 // longer contiguous runs per row (XCH * 240 B), fewer z pairs cost more halo slices (2 ZP + 2 loaded per 2 ZP outputs).
 #ifndef HB_ZP
-#define HB_ZP 8
+#define HB_ZP 4
 #endif
 #ifndef HB_XCH
 #define HB_XCH 1
@@ -448,8 +449,8 @@ void hb_launch_shuffle_stencil( int mode, const HbLevelView& lv, const HbStencil
    const unsigned g = (unsigned) grid, b = PAIRS * 32;
    const int regs = depth / 100; // tuning: 100 * register-budget code + depth
    depth %= 100;
-   if ( depth <= 0 ) // fused-operand modes keep two more ring values per row: one row less in flight fits 128 registers
-      depth = ( mode == HB_APPLY_REPLACE ) ? DEPTH_DEFAULT : 4;
+   if ( depth <= 0 ) // measured best on B200 with 4-warp CTAs (profiles/r1_b_interior_sweeps.txt)
+      depth = 4;
    switch ( depth )
    {
    case 3:
@@ -469,7 +470,7 @@ void hb_launch_shuffle_stencil( int mode, const HbLevelView& lv, const HbStencil
 void hb_shuffle_build_items( int N, std::vector< HbItem >& items, int ys, int order )
 {
    // ys + 2 input rows per item: a multiple of DEPTH_DEFAULT keeps the last unrolled block full
-   const int ZBh = 2 * ZP, YS = ys > 0 ? ys : 48;
+   const int ZBh = 2 * ZP, YS = ys > 0 ? ys : 32;
    items.clear();
    std::vector< long long > work;
    for ( int z0 = 1; z0 <= N - 3; z0 += ZBh )
