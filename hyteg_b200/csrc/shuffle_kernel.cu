@@ -126,9 +126,10 @@ __global__ void __maxnreg__( REGS ) hb_shuffle_kernel( const HbLevelView lv, con
    // independent of each other.  Addresses are opaque 64-bit integers and the accesses are PTX, so the compiler neither
    // re-derives them from indices nor serialises them.
    using u64       = unsigned long long;
-   // sa.sync bits 1,2 are measurement probes (tools/sweep_order.py): all cells read macro-cell 0 / nothing is stored
+   // sa.sync bits 1,2,3 are measurement probes (tools/sweep_order.py): all cells read macro-cell 0 / nothing is stored / all
+   // cells store into macro-cell 0
    const u64 srcB  = (u64) ( sa.srcArena + ( ( sa.sync & 2 ) ? 0 : cellBase ) );
-   const u64 dstB  = (u64) ( a.dst + cellBase );
+   const u64 dstB  = (u64) ( a.dst + ( ( sa.sync & 8 ) ? 0 : cellBase ) ); // probe 8: all cells store into macro-cell 0
    const u64 exB   = EX ? (u64) ( sa.extraArena + cellBase ) : 0ull;
    const int ya    = it.ya, nOut = it.nOut; // CTA-uniform trip count: keeps the shuffles in provably convergent code
    const int rowIn = row_base( N, ya - 1, zA - 1 ) + xc; // slice zA-1, row ya-1

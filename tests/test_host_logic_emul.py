@@ -47,3 +47,37 @@ def test_blas(emul_lib, name):
 @pytest.mark.parametrize("Lc", [0, 1, 2])
 def test_transfer(emul_lib, name, Lc):
     pc.case_transfer(emul_lib, meshes.golden(name), Lc)
+
+
+@pytest.mark.parametrize("name,n_ranks", [("cube_6el", 2), ("cube_24el", 3), ("regular_octahedron_8el", 4)])
+@pytest.mark.parametrize("L", [1, 3])
+def test_exchange_plan_is_symmetric(emul_lib, name, n_ranks, L):
+    """ghost exchange plan: what all ranks send equals what all ranks receive; every rank with a neighbour exchanges something;
+    the mirrored layers are a small fraction of a macro-cell on finer levels"""
+    from hyteg_b200 import api
+    v, c = meshes.golden(name)
+    sent = recv = 0
+    for r in range(n_ranks):
+        st = api.PrimitiveStorage(v, c, r, n_ranks, lib=emul_lib)
+        st.setMeshBoundaryFlagsOnBoundary(1, 0, True)
+        peers, ns, nr = st.exchange_info(L)
+        assert 1 <= peers <= n_ranks - 1
+        assert ns > 0 and nr > 0
+        sent += ns
+        recv += nr
+    assert sent == recv
+
+
+def test_interface_coordinates_identical_in_all_copies(emul_lib):
+    """micro-vertex coordinates of an interface point are bit-identical in every macro-cell that holds a copy, also on a mesh
+    with irrational vertex coordinates (spherical shell): interpolate( expression ) keeps the copies consistent"""
+    from hyteg_b200 import api
+    v, c = meshes.spherical_shell(2, 2)
+    L = 2
+    st = api.PrimitiveStorage(v, c, lib=emul_lib)
+    st.setMeshBoundaryFlagsOnBoundary(1, 0, True)
+    f = api.P1Function("f", st, L, L)
+    f.interpolate(lambda x, y, z: np.sin(3 * x) * np.exp(y) + z * z, L, All)
+    from oracle import p1_oracle as po
+    o = po.P1Oracle(v, c, L, L)
+    o.from_cells(f.download(L), L, check=True, tol=0.0)  # raises if two copies of a DoF differ

@@ -20,15 +20,17 @@ def t(fn, n=reps):
     b.record(s); torch.cuda.synchronize()
     return a.elapsed_time(b) / n * 1e3
 lib.dll.hb_set_tuning(b"apply_parts", 1)
-for ys in (32, 48, 96):
-    for sync in (0,):
-        lib.dll.hb_set_tuning(b"shuffle_ys", ys); lib.dll.hb_set_tuning(b"shuffle_sync", sync)
+for ys in (32,):
+    for sync in (0, 100, 200, 1000, 1100, 1200):  # here: order * 100 + cell_major * 1000 (cell_major inverted: 1000 = item-major)
+        order, itemmajor = (sync // 100) % 10, sync // 1000
+        lib.dll.hb_set_tuning(b"shuffle_ys", ys); lib.dll.hb_set_tuning(b"shuffle_sync", 0)
+        lib.dll.hb_set_tuning(b"shuffle_order", order); lib.dll.hb_set_tuning(b"shuffle_cell_major", 1 - itemmajor)
         st = api.PrimitiveStorage(v, c); st.setMeshBoundaryFlagsOnBoundary(1, 0, True)
         A = api.P1ConstantLaplaceOperator(st, L, L)
         src, dst = api.P1Function("s", st, L, L), api.P1Function("d", st, L, L)
         src.interpolate(1.0, L, hb.All)
         r = []
-        for depth in (4, 5):
+        for depth in (4,):
             lib.dll.hb_set_tuning(b"shuffle_depth", depth)
             r.append("d%d %.1f us" % (depth, t(lambda: A.apply(src, dst, L, hb.All))))
         print("ys", ys, "sync", sync, *r, flush=True)
