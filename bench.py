@@ -18,9 +18,9 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-# dram__bytes_read.sum + dram__bytes_write.sum of one hb_shuffle_kernel<0,5,128> launch at level 8 on cube_6el
-# (ncu --set full capture, profiles/r1_b_apply_v3_ncu_full_summary.txt): 144.4 MB + 93.7 MB
-NCU_TRAFFIC_INTERIOR_L8 = 238.1e6
+# dram__bytes_read.sum + dram__bytes_write.sum of one hb_shuffle_kernel<0,4,128> launch at level 8 on cube_6el
+# (ncu --set full capture, profiles/r1_c_apply_final_ncu_full_summary.txt): 143.2 MB + 93.1 MB
+NCU_TRAFFIC_INTERIOR_L8 = 236.3e6
 BYTES_PER_DOF = {"apply": 16.0, "jacobi": 24.0, "sor": 24.0}  # algorithmic: src+dst / src+rhs+dst
 
 
@@ -304,7 +304,7 @@ def main():
                            "multi_gpu": "macro-cells partitioned, ghost layers over NCCL" if world > 1 else "single"},
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                              "traffic": NCU_TRAFFIC_INTERIOR_L8 if L == 8 else None, "peak_source": which,
-                             "kernel": "hb_shuffle_kernel<APPLY_REPLACE,5,128> (interior points of all local macro-cells, one launch)",
+                             "kernel": "hb_shuffle_kernel<APPLY_REPLACE,4,128> (interior points of all local macro-cells, one launch)",
                              "algorithmic_bytes_per_launch": BYTES_PER_DOF["apply"] * n_interior, "us_per_launch": 1e3 * ms_interior,
                              "share_of_step": ms_interior / ms_apply,
                              "whole_apply": {"achieved": whole, "frac": whole / peak,
