@@ -142,6 +142,9 @@ __device__ __forceinline__ void hb_boundary_block( const HbLevelView& lv, const 
       return;
    if ( !( ( a.dimSel >> reg.dim ) & 1 ) )
       return;
+   // dimSel bit 4: only primitives whose macro-cells all live on this rank; bit 5: only primitives shared with other ranks
+   if ( ( ( a.dimSel & 16 ) && ( reg.owner & 4 ) ) || ( ( a.dimSel & 32 ) && !( reg.owner & 4 ) ) )
+      return;
    if ( (int) threadIdx.x >= ch.count )
       return;
    const int        i = ch.first + threadIdx.x;
@@ -194,6 +197,8 @@ __device__ __forceinline__ void hb_boundary_block_desc( const HbLevelView& lv, c
    __syncthreads();
    if ( !( sd.owner & 2 ) || !( ( a.selMask >> sd.bflag ) & 1 ) || !( ( a.dimSel >> sd.dim ) & 1 ) )
       return; // block-uniform
+   if ( ( ( a.dimSel & 16 ) && ( sd.owner & 4 ) ) || ( ( a.dimSel & 32 ) && !( sd.owner & 4 ) ) )
+      return;
    const int nC = sd.nCopies;
    if ( nC > HB_DESC_MAXC )
    {

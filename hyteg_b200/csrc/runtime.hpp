@@ -114,6 +114,8 @@ struct hb_function
    std::vector< hb::DeviceBuffer< double* > > cellPtr; // per level: [nSlots] device pointers
    std::vector< char > mirrorsStale;                   // per level: mirrored cells do not hold the owners' current values
    void touched( int L ) { mirrorsStale[L - minLevel] = 1; } // call after every write to the level's arena
+   bool stale( int L ) const { return st_nranks() > 1 && mirrorsStale[L - minLevel] != 0; }
+   int  st_nranks() const;
    void syncMirrors( int L );                                // ghost exchange if stale (no-op on one rank)
    double*        arena( int L ) const;
    double* const* ptrs( int L ) const;

@@ -209,6 +209,34 @@ static int localMinCell( const Topology& topo, int g, int m, int rank )
    return best;
 }
 
+// true if some macro-cell containing the macro primitive 'region m' of macro-cell g belongs to another rank
+static bool hasRemoteCell( const Topology& topo, int g, int m, int rank )
+{
+   static const int faceBitOfB[4] = { 8, 1, 2, 4 };
+   int              supp[4], ns = 0;
+   for ( int j = 0; j < 4; j++ )
+      if ( !( m & faceBitOfB[j] ) )
+         supp[ns++] = topo.cellV[g][j];
+   if ( ns == 0 )
+      return false;
+   for ( int c : topo.vCells[supp[0]] )
+   {
+      if ( topo.cellRank[c] == rank )
+         continue;
+      bool all = true;
+      for ( int k = 1; k < ns && all; k++ )
+      {
+         bool has = false;
+         for ( int j = 0; j < 4; j++ )
+            has = has || topo.cellV[c][j] == supp[k];
+         all = has;
+      }
+      if ( all )
+         return true;
+   }
+   return false;
+}
+
 uint32_t sharedRegionMasks( const Topology& topo, int g, int rank )
 {
    static const int faceBitOfB[4] = { 8, 1, 2, 4 }; // local vertex j is OFF the face with this mask bit
@@ -309,6 +337,9 @@ void LocalView::build( const Topology& topo, int rank_, int nRanks_ )
             r.owner = 3;
          else if ( dim <= 2 && localMinCell( topo, c, m, rank ) == c )
             r.owner |= 2;
+         // bit 2: the primitive is shared with another rank (its stencil reads mirrored data: needs a current ghost layer)
+         if ( dim <= 2 && nRanks > 1 && hasRemoteCell( topo, c, m, rank ) )
+            r.owner |= 4;
       }
    };
    for ( int l = 0; l < nLocal; l++ )
