@@ -497,7 +497,8 @@ __device__ __forceinline__ void hb_commit_block( const HbLevelView& lv, const Hb
    }
 }
 
-__global__ void __launch_bounds__( HB_BLOCK, 4 ) hb_sor_interface_coop_kernel( const HbLevelView lv, HbStencilArgs a, const int backwards )
+__global__ void __launch_bounds__( HB_BLOCK, 4 )
+    hb_sor_interface_coop_kernel( const HbLevelView lv, HbStencilArgs a, const int backwards, const int kLo, const int kHi )
 {
    cooperative_groups::grid_group grid = cooperative_groups::this_grid();
    const int nBlk = lv.nCells * lv.nChunks;
@@ -505,6 +506,8 @@ __global__ void __launch_bounds__( HB_BLOCK, 4 ) hb_sor_interface_coop_kernel( c
    for ( int ph = 0; ph < 6; ph++ )
    {
       const int k   = backwards ? 5 - ph : ph;          // phases 0: vertices | 1,2: edges | 3,4,5: faces
+      if ( k < kLo || k > kHi )
+         continue;
       const int dim = k == 0 ? 0 : ( k <= 2 ? 1 : 2 );
       a.dimSel      = 1 << dim;
       a.bndColour   = k == 0 ? 0 : ( k <= 2 ? k - 1 : k - 3 );
@@ -518,7 +521,7 @@ __global__ void __launch_bounds__( HB_BLOCK, 4 ) hb_sor_interface_coop_kernel( c
 }
 #endif
 
-bool hb_launch_sor_interface_coop( const HbLevelView& lv, const HbStencilArgs& a, int backwards, cudaStream_t st )
+bool hb_launch_sor_interface_coop( const HbLevelView& lv, const HbStencilArgs& a, int backwards, int kLo, int kHi, cudaStream_t st )
 {
 #ifdef HB_EMUL
    return false;
@@ -544,7 +547,7 @@ bool hb_launch_sor_interface_coop( const HbLevelView& lv, const HbStencilArgs& a
    HbLevelView   lvc = lv;
    HbStencilArgs ac  = a;
    int           bw  = backwards;
-   void*         args[] = { &lvc, &ac, &bw };
+   void*         args[] = { &lvc, &ac, &bw, &kLo, &kHi };
    return cudaLaunchCooperativeKernel( (void*) hb_sor_interface_coop_kernel, dim3( grid ), dim3( HB_BLOCK ), args, 0, st ) == cudaSuccess;
 #endif
 }

@@ -33,6 +33,7 @@ void hb_launch_pack( const double* arena, const long long* off, long long n, dou
 void hb_launch_unpack( double* arena, const long long* off, long long n, const double* buf, cudaStream_t st );
 // whole SOR sweep of a small level in one single-CTA launch; false if the level is too large (or in the emulation build)
 bool hb_launch_sor_small( const HbLevelView& lv, const HbStencilArgs& a, int backwards, cudaStream_t st );
-// the six interface phases (+ commits) of an SOR sweep in one cooperative launch; false if unavailable
-bool hb_launch_sor_interface_coop( const HbLevelView& lv, const HbStencilArgs& a, int backwards, cudaStream_t st );
+// interface phases kLo..kHi (0 vertices | 1,2 edge colours | 3,4,5 face colours; + commits) of an SOR sweep in one cooperative
+// launch; false if unavailable
+bool hb_launch_sor_interface_coop( const HbLevelView& lv, const HbStencilArgs& a, int backwards, int kLo, int kHi, cudaStream_t st );
 extern int hb_use_desc; // 1: interface kernel reads per-block descriptors, 0: walks the topology tables (default)

@@ -277,10 +277,11 @@ def test_sor_cooperative_interface_matches_multi_launch(cuda_lib, name, L):
         return x.download(L)
 
     try:
-        a, g = run(1), run(0)
+        a, h, g = run(1), run(2), run(0)  # all phases cooperative / vertex + edge phases only / one launch per phase
     finally:
         cuda_lib.dll.hb_set_tuning(b"sor_coop", -2147483648)
     assert np.array_equal(a, g), np.abs(a - g).max()
+    assert np.array_equal(h, g), np.abs(h - g).max()
 
 
 @pytest.mark.parametrize("name,L", [("cube_6el", 5), ("regular_octahedron_8el", 5), ("cube_24el", 5)])
