@@ -874,11 +874,36 @@ __device__ __forceinline__ double hb_restrict_partial( const HbLevelView& fine, 
    return acc;
 }
 
-__global__ void hb_restrict_kernel( const HbLevelView coarse, const HbLevelView fine, const double* const* fsrc, double* cdst, const HbBC bc, int flag )
+// interface coarse point (cell, x, y, z): sum over the macro-cells containing it (additive communication of the reference)
+__device__ __forceinline__ double hb_restrict_interface( const HbLevelView& coarse, const HbLevelView& fine, const double* const* fsrc, const HbCellInfo* ci, int x, int y, int z )
+{
+   const int N    = coarse.N;
+   const int b[4] = { N - x - y - z, x, y, z };
+   int       supp = 0;
+   for ( int j = 0; j < 4; j++ )
+      supp |= ( b[j] != 0 ) << j;
+   double acc = 0.0;
+   for ( int e = ci->copyBegin; e < ci->copyEnd; e++ )
+   {
+      const HbCopy cp = coarse.copies[e];
+      if ( supp & ~cp.sharedMask )
+         continue;
+      int bp[4] = { 0, 0, 0, 0 };
+      for ( int j = 0; j < 4; j++ )
+         if ( ( supp >> j ) & 1 )
+            bp[cp.vmap[j]] = b[j];
+      acc += hb_restrict_partial( fine, fsrc[cp.slot], cp.slot, bp[1], bp[2], bp[3] );
+   }
+   return acc;
+}
+
+// pass 1: interior coarse points (flat over the arena; interface points are skipped -- or, with doInterface, handled in place:
+// emulation build and tiny levels).  pass 2 (hb_restrict_interface_kernel): the compact interface point list, so that the long
+// interface path does not drag every warp of pass 1 along (each row of the tetrahedral layout starts and ends on an interface).
+__global__ void hb_restrict_kernel( const HbLevelView coarse, const HbLevelView fine, const double* const* fsrc, double* cdst, const HbBC bc, int flag, int doInterface )
 {
    const size_t n      = (size_t) coarse.nCells * coarse.cellSize;
    const size_t stride = (size_t) gridDim.x * blockDim.x;
-   const int    N      = coarse.N;
    for ( size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride )
    {
       const int         cell  = (int) ( i / (size_t) coarse.cellSize );
@@ -887,6 +912,8 @@ __global__ void hb_restrict_kernel( const HbLevelView coarse, const HbLevelView 
       const int         x = q.x, y = q.y, z = q.z;
       const int         m  = q.mask;
       const HbCellInfo* ci = coarse.cells + cell;
+      if ( m != 0 && !doInterface )
+         continue;
       if ( !( bc.type[ci->region[m].bflag] & flag ) )
          continue;
       double acc = 0.0;
@@ -917,24 +944,23 @@ __global__ void hb_restrict_kernel( const HbLevelView coarse, const HbLevelView 
          acc += 0.5 * f[i0 + dBN - 1];  // BNW
       }
       else
-      {
-         const int b[4] = { N - x - y - z, x, y, z };
-         int       supp = 0;
-         for ( int j = 0; j < 4; j++ )
-            supp |= ( b[j] != 0 ) << j;
-         for ( int e = ci->copyBegin; e < ci->copyEnd; e++ )
-         {
-            const HbCopy cp = coarse.copies[e];
-            if ( supp & ~cp.sharedMask )
-               continue;
-            int bp[4] = { 0, 0, 0, 0 };
-            for ( int j = 0; j < 4; j++ )
-               if ( ( supp >> j ) & 1 )
-                  bp[cp.vmap[j]] = b[j];
-            acc += hb_restrict_partial( fine, fsrc[cp.slot], cp.slot, bp[1], bp[2], bp[3] );
-         }
-      }
+         acc = hb_restrict_interface( coarse, fine, fsrc, ci, x, y, z );
       cdst[i] = acc;
+   }
+}
+
+__global__ void hb_restrict_interface_kernel( const HbLevelView coarse, const HbLevelView fine, const double* const* fsrc, double* cdst, const HbBC bc, int flag )
+{
+   const long long n      = (long long) coarse.nCells * coarse.nBnd;
+   const long long stride = (long long) gridDim.x * blockDim.x;
+   for ( long long item = (long long) blockIdx.x * blockDim.x + threadIdx.x; item < n; item += stride )
+   {
+      const int         cell = (int) ( item / coarse.nBnd );
+      const HbBndPoint  p    = coarse.bnd[item - (long long) cell * coarse.nBnd];
+      const HbCellInfo* ci   = coarse.cells + cell;
+      if ( !( bc.type[ci->region[p.mask].bflag] & flag ) )
+         continue;
+      cdst[(size_t) cell * coarse.cellSize + hb_index( coarse.N, p.x, p.y, p.z )] = hb_restrict_interface( coarse, fine, fsrc, ci, p.x, p.y, p.z );
    }
 }
 
@@ -988,7 +1014,14 @@ void hb_launch_restrict( const HbLevelView& coarse, const HbLevelView& fine, con
    const size_t n = (size_t) coarse.nCells * coarse.cellSize;
    if ( n == 0 )
       return;
-   HB_LAUNCH( hb_restrict_kernel, hb_flat_grid( n, 256, 148 * 16 ), 256, st, coarse, fine, fsrc, cdst, bc, flag );
+#ifdef HB_EMUL
+   const bool twoPass = false;
+#else
+   const bool twoPass = coarse.N >= 16;
+#endif
+   HB_LAUNCH( hb_restrict_kernel, hb_flat_grid( n, 256, 148 * 16 ), 256, st, coarse, fine, fsrc, cdst, bc, flag, twoPass ? 0 : 1 );
+   if ( twoPass )
+      HB_LAUNCH( hb_restrict_interface_kernel, hb_flat_grid( (size_t) coarse.nCells * coarse.nBnd, 128, 148 * 16 ), 128, st, coarse, fine, fsrc, cdst, bc, flag );
 }
 
 void hb_launch_prolongate( const HbLevelView& coarse, const HbLevelView& fine, const double* csrc, double* fdst, const HbBC& bc, int flag, int add, cudaStream_t st )
