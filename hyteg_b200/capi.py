@@ -34,6 +34,10 @@ _SIGNATURES = {
     "hb_nccl_unique_id": (C.c_int, [_vp]),
     "hb_nccl_init": (C.c_int, [_vp, C.c_int, C.c_int]),
     "hb_nccl_finalize": (C.c_int, []),
+    "hb_p2p_window": (C.c_int, [_vp, C.c_longlong, C.c_int]),
+    "hb_p2p_connect": (C.c_int, [_vp, C.c_int, C.c_int]),
+    "hb_p2p_finalize": (C.c_int, []),
+    "hb_p2p_active": (C.c_int, [C.POINTER(C.c_longlong)]),
     "hb_set_exchange": (C.c_int, [_vp, _vp]),
     "hb_exchange_stats": (C.c_int, [C.POINTER(C.c_longlong), C.POINTER(C.c_longlong)]),
     "hb_storage_exchange_info": (C.c_int, [_vp, C.c_int, _ip, C.POINTER(C.c_longlong), C.POINTER(C.c_longlong)]),

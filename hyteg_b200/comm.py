@@ -6,6 +6,8 @@ csrc/runtime_comm.inc); torch.distributed only broadcasts the NCCL unique id.  W
 through callbacks into torch.distributed instead.
 """
 import ctypes as C
+import os
+import sys
 
 import numpy as np
 
@@ -14,8 +16,9 @@ _EXCHANGE_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int, C.POINTER(C.c_int), C.P
 _ALLREDUCE_FN = C.CFUNCTYPE(None, C.POINTER(C.c_double), C.c_int, C.c_int, C.c_void_p)
 
 
-def init_nccl(lib):
-    """Creates the library's NCCL communicator over the ranks of the default torch.distributed group."""
+def init_nccl(lib, p2p=None, segment_bytes=32 << 20):
+    """Creates the library's NCCL communicator over the ranks of the default torch.distributed group and, unless
+    p2p is False (or HB_P2P=0), the peer-memory windows for the ghost exchange (all ranks on one node)."""
     import torch
     import torch.distributed as dist
     rank, world = dist.get_rank(), dist.get_world_size()
@@ -27,6 +30,40 @@ def init_nccl(lib):
     raw = bytes(t.cpu().tolist())
     buf = (C.c_char * 128).from_buffer_copy(raw)
     lib.check(lib.dll.hb_nccl_init(C.cast(buf, C.c_void_p), rank, world))
+    if p2p is None:
+        p2p = os.environ.get("HB_P2P", "1") != "0"
+    if p2p and world > 1:
+        init_p2p(lib, segment_bytes)
+
+
+def init_p2p(lib, segment_bytes=32 << 20):
+    """Peer-memory windows: all-gather of the CUDA IPC handles, then every rank maps its neighbours' windows.
+    Falls back (on every rank together, with a message) to the NCCL send/recv exchange if any rank cannot map."""
+    import torch
+    import torch.distributed as dist
+    rank, world = dist.get_rank(), dist.get_world_size()
+    handle = (C.c_char * 64)()
+    ok = lib.dll.hb_p2p_window(C.cast(handle, C.c_void_p), segment_bytes, world) == 0
+    mine = torch.tensor(list(handle.raw), dtype=torch.uint8, device="cuda")
+    every = [torch.empty_like(mine) for _ in range(world)]
+    dist.all_gather(every, mine)
+    if ok:
+        raw = b"".join(bytes(t.cpu().tolist()) for t in every)
+        buf = (C.c_char * (64 * world)).from_buffer_copy(raw)
+        ok = lib.dll.hb_p2p_connect(C.cast(buf, C.c_void_p), rank, world) == 0
+    flag = torch.tensor([1 if ok else 0], device="cuda")
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    if int(flag.item()) == 0:
+        lib.dll.hb_p2p_finalize()
+        if rank == 0:
+            print("hyteg_b200: peer-memory windows unavailable (%s); ghost exchange stays on NCCL send/recv" % lib.dll.hb_last_error().decode(), file=sys.stderr)
+        return False
+    return True
+
+
+def p2p_active(lib):
+    n = C.c_longlong(0)
+    return bool(lib.dll.hb_p2p_active(C.byref(n))), n.value
 
 
 def init_callbacks(lib):

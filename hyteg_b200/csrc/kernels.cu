@@ -369,13 +369,164 @@ __global__ void hb_commit_kernel( const HbLevelView lv, const HbStencilArgs a )
    }
 }
 
+#ifndef HB_EMUL
+// =============================================================================================
+//  Ghost exchange over NVLink peer memory
+// =============================================================================================
+// The ack word only says "the lines of message n have been read": the reads completed (their values were stored to the arena and a
+// barrier passed) before the ack store is issued, and the waiting side orders nothing but its own later stores after the poll --
+// so plain volatile (relaxed, L1-bypassing) accesses do; a release store here would stall on the thread's outstanding NVLink puts.
+__device__ __forceinline__ unsigned long long hb_ld_word( const unsigned long long* p )
+{
+   unsigned long long v;
+   asm volatile( "ld.volatile.global.u64 %0, [%1];" : "=l"( v ) : "l"( p ) : "memory" );
+   return v;
+}
+__device__ __forceinline__ void hb_st_word( unsigned long long* p, unsigned long long v )
+{
+   asm volatile( "st.volatile.global.u64 [%0], %1;" ::"l"( p ), "l"( v ) : "memory" );
+}
+__device__ __forceinline__ bool hb_p2p_sends( const HbP2PArgs& p, int k ) { return p.sendStart[k + 1] > p.sendStart[k]; }
+__device__ __forceinline__ bool hb_p2p_recvs( const HbP2PArgs& p, int k ) { return p.recvStart[k + 1] > p.recvStart[k]; }
+#define HB_P2P_SPIN_LIMIT ( 1u << 27 ) // polls before a waiting kernel gives up (trap) instead of hanging the GPU: > 10 s
+
+// Wire format: every double travels as one 16-byte line { lo, tag, hi, tag } (tag = low 32 bits of the pair's message number),
+// written with one vector store; the receiver polls the line itself until both tags match.  Data and "it has landed" arrive
+// together -- no system fence and no separate flag round trip on the critical path.  (8-byte single-copy atomicity of the two
+// { half, tag } pairs is all this needs; the scheme is the one NCCL's LL protocol uses.)
+__device__ __forceinline__ void hb_p2p_store_line( HbP2PLine* line, double v, unsigned tag )
+{
+   const unsigned long long b = (unsigned long long) __double_as_longlong( v );
+   asm volatile( "st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"( line ), "r"( (unsigned) b ), "r"( tag ), "r"( (unsigned) ( b >> 32 ) ), "r"( tag ) : "memory" );
+}
+__device__ __forceinline__ double hb_p2p_load_line( const HbP2PLine* line, unsigned tag )
+{
+   unsigned lo, t0, hi, t1, spins = 0;
+   do
+   {
+      asm volatile( "ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"( lo ), "=r"( t0 ), "=r"( hi ), "=r"( t1 ) : "l"( line ) : "memory" );
+      if ( ++spins > HB_P2P_SPIN_LIMIT )
+         __trap(); // the neighbour never sent this message (ranks out of step, or a rank died)
+   } while ( t0 != tag || t1 != tag );
+   return __longlong_as_double( (long long) ( ( (unsigned long long) hi << 32 ) | lo ) );
+}
+
+// message m of this launch may go into its window slot once message m-2 of the pair (same slot) has been unpacked over there
+__device__ __forceinline__ void hb_p2p_wait_slot( const HbP2PArgs& p, unsigned m )
+{
+   const int k = threadIdx.x;
+   if ( k < p.np && hb_p2p_sends( p, k ) && p.sendSeq[k] + m > 2 )
+   {
+      unsigned spins = 0;
+      while ( hb_ld_word( p.localAck[k] ) + 2 < p.sendSeq[k] + m )
+         if ( ++spins > HB_P2P_SPIN_LIMIT )
+            __trap();
+   }
+   __syncthreads();
+}
+__device__ __forceinline__ void hb_p2p_put( const double* arena, const long long* __restrict__ sendOff, const HbP2PArgs& p, unsigned m, long long t0, long long stride )
+{
+   const long long nS = p.sendStart[p.np];
+   for ( long long i = t0; i < nS; i += stride )
+   {
+      int k = 0;
+      while ( i >= p.sendStart[k + 1] )
+         k++;
+      const unsigned long long seq = p.sendSeq[k] + m;
+      HbP2PLine*                   slot = p.remoteData[k] + ( ( seq & 1 ) ? p.segLines : 0 );
+      hb_p2p_store_line( slot + ( i - p.sendStart[k] ), arena[sendOff[i]], (unsigned) seq );
+   }
+}
+__device__ __forceinline__ void hb_p2p_get( double* arena, const long long* __restrict__ recvOff, const HbP2PArgs& p, unsigned m, long long t0, long long stride )
+{
+   const long long nR = p.recvStart[p.np];
+   for ( long long j = t0; j < nR; j += stride )
+   {
+      int k = 0;
+      while ( j >= p.recvStart[k + 1] )
+         k++;
+      const unsigned long long seq  = p.recvSeq[k] + m;
+      const HbP2PLine*             slot = p.localData[k] + ( ( seq & 1 ) ? p.segLines : 0 );
+      arena[recvOff[j]]             = hb_p2p_load_line( slot + ( j - p.recvStart[k] ), (unsigned) seq );
+   }
+}
+// one CTA, after every get of the grid is done: the slot may be overwritten (by message m+2)
+__device__ __forceinline__ void hb_p2p_ack( const HbP2PArgs& p, unsigned m )
+{
+   const int k = threadIdx.x;
+   if ( k < p.np && hb_p2p_recvs( p, k ) )
+      hb_st_word( p.remoteAck[k], p.recvSeq[k] + m );
+}
+
+// exchange number m of a launch from INSIDE a kernel whose CTAs can synchronise through bar() (block barrier of a single-CTA
+// kernel, grid barrier of a cooperative launch): everything written to the arena before the call travels
+template < class Bar >
+__device__ __forceinline__ void hb_p2p_exchange_inline( double* arena, const HbP2PArgs& p, unsigned m, Bar bar )
+{
+   const long long t0 = (long long) blockIdx.x * blockDim.x + threadIdx.x, stride = (long long) gridDim.x * blockDim.x;
+   bar();
+   hb_p2p_wait_slot( p, m );
+   hb_p2p_put( arena, p.sendOff, p, m, t0, stride );
+   hb_p2p_get( arena, p.recvOff, p, m, t0, stride );
+   __threadfence();
+   bar();
+   if ( blockIdx.x == 0 )
+      hb_p2p_ack( p, m );
+}
+
+// Ghost exchange in one kernel (replaces pack -> ncclSend/ncclRecv -> unpack; same data, same layout):
+//   put : arena[sendOff[i]] -> lines in the neighbour's window (remote stores over NVLink)
+//   get : poll the lines the neighbours write here, -> arena[recvOff[j]]; the last CTA acks
+// Windows are double-buffered per pair.  No CTA waits on another CTA of its own grid, so the grid need not be co-resident; a
+// neighbour's put never waits on this rank's current kernel.
+__global__ void __launch_bounds__( 256 ) hb_p2p_exchange_kernel( double* arena, const HbP2PArgs p )
+{
+   __shared__ int  last;
+   const long long stride = (long long) gridDim.x * blockDim.x;
+   const long long t0     = (long long) blockIdx.x * blockDim.x + threadIdx.x;
+   hb_p2p_wait_slot( p, 0 );
+   hb_p2p_put( arena, p.sendOff, p, 0, t0, stride );
+   hb_p2p_get( arena, p.recvOff, p, 0, t0, stride );
+   __syncthreads();
+   if ( threadIdx.x == 0 )
+      last = atomicAdd( p.counters, 1u ) == gridDim.x - 1;
+   __syncthreads();
+   if ( last )
+   {
+      hb_p2p_ack( p, 0 );
+      if ( threadIdx.x == 0 )
+         p.counters[0] = 0;
+   }
+}
+#endif
+
+void hb_launch_p2p_exchange( double* arena, const HbP2PArgs& p, cudaStream_t st )
+{
+#ifndef HB_EMUL
+   const long long n    = p.sendStart[p.np] > p.recvStart[p.np] ? p.sendStart[p.np] : p.recvStart[p.np];
+   long long       grid = ( n + 1023 ) / 1024; // 4 elements per thread
+   if ( grid < 1 )
+      grid = 1;
+   if ( grid > 148 )
+      grid = 148;
+   hb_p2p_exchange_kernel<<< (unsigned) grid, 256, 0, st >>>( arena, p );
+#endif
+}
+
 // Whole SOR sweep of a SMALL level in one launch: a single CTA walks the phases of hb_operator_smooth_sor (macro vertices,
 // edges in 2 colours, faces in 3 colours, each staged through scratch and committed; then the 4 interior colours) with a
 // block barrier in between.  The coarse levels of a V-cycle are launch-latency bound: 16 launches per sweep become one.
 // Same arithmetic, in the same order, as the multi-launch path (hb_boundary_block / hb_interior_tile).
 #ifndef HB_EMUL
-__global__ void __launch_bounds__( 1024 ) hb_sor_small_kernel( const HbLevelView lv, HbStencilArgs a, const int backwards )
+__global__ void __launch_bounds__( 1024 ) hb_sor_small_kernel( const HbLevelView lv, HbStencilArgs a, const int backwards, const HbP2PArgs px )
 {
+   // more than one rank (px.np > 0): the ghost exchanges of the sweep happen in here as well, over the peer-memory windows --
+   // after every interface phase but the last one, and (backward sweep) between the interior and the interface phases
+   unsigned m        = 0;
+   auto     exchange = [&]() {
+      if ( px.np > 0 )
+         hb_p2p_exchange_inline( a.dst, px, m++, [] { __syncthreads(); } );
+   };
    const int       N      = lv.N;
    const long long nItems = (long long) lv.nCells * lv.nBnd;
    const long long nAll   = (long long) lv.nCells * lv.cellSize;
@@ -453,7 +604,11 @@ __global__ void __launch_bounds__( 1024 ) hb_sor_small_kernel( const HbLevelView
    {
       for ( int d = 0; d <= 2; d++ )
          for ( int c = 0; c < nColours[d]; c++ )
+         {
             interfacePhase( d, c );
+            if ( !( d == 2 && c == 2 ) )
+               exchange();
+         }
       for ( int c = 0; c < 4; c++ )
          interiorPhase( c );
    }
@@ -461,9 +616,14 @@ __global__ void __launch_bounds__( 1024 ) hb_sor_small_kernel( const HbLevelView
    {
       for ( int c = 3; c >= 0; c-- )
          interiorPhase( c );
+      exchange();
       for ( int d = 2; d >= 0; d-- )
          for ( int c = nColours[d] - 1; c >= 0; c-- )
+         {
             interfacePhase( d, c );
+            if ( d != 0 )
+               exchange();
+         }
    }
 }
 #endif
@@ -498,9 +658,10 @@ __device__ __forceinline__ void hb_commit_block( const HbLevelView& lv, const Hb
 }
 
 __global__ void __launch_bounds__( HB_BLOCK, 4 )
-    hb_sor_interface_coop_kernel( const HbLevelView lv, HbStencilArgs a, const int backwards, const int kLo, const int kHi )
+    hb_sor_interface_coop_kernel( const HbLevelView lv, HbStencilArgs a, const int backwards, const int kLo, const int kHi, const HbP2PArgs px )
 {
    cooperative_groups::grid_group grid = cooperative_groups::this_grid();
+   unsigned                       m    = 0; // more than one rank (px.np > 0): ghost exchange after every phase but the sweep's last
    const int nBlk = lv.nCells * lv.nChunks;
    a.toScratch    = 1;
    for ( int ph = 0; ph < 6; ph++ )
@@ -516,28 +677,43 @@ __global__ void __launch_bounds__( HB_BLOCK, 4 )
       grid.sync();
       for ( int blk = blockIdx.x; blk < nBlk; blk += gridDim.x )
          hb_commit_block( lv, a, blk );
-      grid.sync();
+      if ( px.np > 0 && k != ( backwards ? 0 : 5 ) )
+         hb_p2p_exchange_inline( a.dst, px, m++, [&] { grid.sync(); } ); // starts and ends with a grid barrier
+      else
+         grid.sync();
    }
 }
 #endif
 
-bool hb_launch_sor_interface_coop( const HbLevelView& lv, const HbStencilArgs& a, int backwards, int kLo, int kHi, cudaStream_t st )
+#ifndef HB_EMUL
+static int hb_coop_per_sm = -1, hb_coop_sms = 0;
+#endif
+bool hb_sor_coop_available()
 {
 #ifdef HB_EMUL
    return false;
 #else
-   static int perSm = -1, nSm = 0, coop = 0;
-   if ( perSm < 0 )
+   if ( hb_coop_per_sm < 0 )
    {
-      int dev = 0;
+      int dev = 0, coop = 0;
       cudaGetDevice( &dev );
-      cudaDeviceGetAttribute( &nSm, cudaDevAttrMultiProcessorCount, dev );
+      cudaDeviceGetAttribute( &hb_coop_sms, cudaDevAttrMultiProcessorCount, dev );
       cudaDeviceGetAttribute( &coop, cudaDevAttrCooperativeLaunch, dev );
-      if ( cudaOccupancyMaxActiveBlocksPerMultiprocessor( &perSm, hb_sor_interface_coop_kernel, HB_BLOCK, 0 ) != cudaSuccess )
-         perSm = 0;
+      if ( !coop || cudaOccupancyMaxActiveBlocksPerMultiprocessor( &hb_coop_per_sm, hb_sor_interface_coop_kernel, HB_BLOCK, 0 ) != cudaSuccess )
+         hb_coop_per_sm = 0;
    }
-   if ( !coop || perSm < 1 )
+   return hb_coop_per_sm >= 1;
+#endif
+}
+
+bool hb_launch_sor_interface_coop( const HbLevelView& lv, const HbStencilArgs& a, int backwards, int kLo, int kHi, const HbP2PArgs& px, cudaStream_t st )
+{
+#ifdef HB_EMUL
+   return false;
+#else
+   if ( !hb_sor_coop_available() )
       return false;
+   const int nSm = hb_coop_sms, perSm = hb_coop_per_sm;
    const int nBlk = lv.nCells * lv.nChunks;
    int       grid = nSm * perSm;
    if ( grid > nBlk )
@@ -547,19 +723,29 @@ bool hb_launch_sor_interface_coop( const HbLevelView& lv, const HbStencilArgs& a
    HbLevelView   lvc = lv;
    HbStencilArgs ac  = a;
    int           bw  = backwards;
-   void*         args[] = { &lvc, &ac, &bw, &kLo, &kHi };
+   HbP2PArgs     pxc = px;
+   void*         args[] = { &lvc, &ac, &bw, &kLo, &kHi, &pxc };
    return cudaLaunchCooperativeKernel( (void*) hb_sor_interface_coop_kernel, dim3( grid ), dim3( HB_BLOCK ), args, 0, st ) == cudaSuccess;
 #endif
 }
 
-bool hb_launch_sor_small( const HbLevelView& lv, const HbStencilArgs& a, int backwards, cudaStream_t st )
+bool hb_sor_small_fits( const HbLevelView& lv )
+{
+#ifdef HB_EMUL
+   return false;
+#else
+   return (long long) lv.nCells * lv.cellSize <= 16384;
+#endif
+}
+
+bool hb_launch_sor_small( const HbLevelView& lv, const HbStencilArgs& a, int backwards, const HbP2PArgs& px, cudaStream_t st )
 {
 #ifdef HB_EMUL
    return false;
 #else
    if ( (long long) lv.nCells * lv.cellSize > 16384 )
       return false; // more than 16 strided passes per interior colour: the multi-launch path wins
-   hb_sor_small_kernel<<< 1, 1024, 0, st >>>( lv, a, backwards );
+   hb_sor_small_kernel<<< 1, 1024, 0, st >>>( lv, a, backwards, px );
    return true;
 #endif
 }

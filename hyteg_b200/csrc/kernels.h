@@ -31,9 +31,35 @@ void hb_launch_prolongate( const HbLevelView& coarse, const HbLevelView& fine, c
 // ghost exchange: buf[i] = arena[off[i]] / arena[off[i]] = buf[i]
 void hb_launch_pack( const double* arena, const long long* off, long long n, double* buf, cudaStream_t st );
 void hb_launch_unpack( double* arena, const long long* off, long long n, const double* buf, cudaStream_t st );
+// ghost exchange over peer memory (NVLink): one kernel packs the layers straight into the neighbours' windows as 16-byte
+// { lo, tag, hi, tag } lines and unpacks the lines the neighbours write here as they land.  All pointers are device addresses;
+// "remote" ones are windows of other GPUs mapped through CUDA IPC (runtime_comm.inc).
+#define HB_P2P_MAXPEERS 8
+struct alignas( 16 ) HbP2PLine
+{
+   uint32_t lo, tag0, hi, tag1;
+};
+struct HbP2PArgs
+{
+   int32_t             np;
+   long long           sendStart[HB_P2P_MAXPEERS + 1], recvStart[HB_P2P_MAXPEERS + 1];
+   const long long*    sendOff;                     // arena offsets of the layers that travel / that arrive (Exchange tables)
+   const long long*    recvOff;
+   long long           segLines;                    // distance between the two slots of a pair, in 16-byte lines
+   HbP2PLine*              remoteData[HB_P2P_MAXPEERS]; // neighbour's window for this rank's messages (slot 0; message n uses slot n & 1)
+   unsigned long long* remoteAck[HB_P2P_MAXPEERS];  // neighbour's "message n to this rank has been unpacked"
+   const HbP2PLine*              localData[HB_P2P_MAXPEERS];
+   const unsigned long long* localAck[HB_P2P_MAXPEERS];
+   unsigned long long  sendSeq[HB_P2P_MAXPEERS], recvSeq[HB_P2P_MAXPEERS]; // 1-based numbers of the launch's first message
+   unsigned int*       counters;                                           // [2], zero between launches
+};
+void hb_launch_p2p_exchange( double* arena, const HbP2PArgs& p, cudaStream_t st );
 // whole SOR sweep of a small level in one single-CTA launch; false if the level is too large (or in the emulation build)
-bool hb_launch_sor_small( const HbLevelView& lv, const HbStencilArgs& a, int backwards, cudaStream_t st );
+// (px.np > 0: more than one rank, the sweep's ghost exchanges run inside the kernel over the peer-memory windows)
+bool hb_sor_small_fits( const HbLevelView& lv );
+bool hb_launch_sor_small( const HbLevelView& lv, const HbStencilArgs& a, int backwards, const HbP2PArgs& px, cudaStream_t st );
 // interface phases kLo..kHi (0 vertices | 1,2 edge colours | 3,4,5 face colours; + commits) of an SOR sweep in one cooperative
 // launch; false if unavailable
-bool hb_launch_sor_interface_coop( const HbLevelView& lv, const HbStencilArgs& a, int backwards, int kLo, int kHi, cudaStream_t st );
+bool hb_sor_coop_available();
+bool hb_launch_sor_interface_coop( const HbLevelView& lv, const HbStencilArgs& a, int backwards, int kLo, int kHi, const HbP2PArgs& px, cudaStream_t st );
 extern int hb_use_desc; // 1: interface kernel reads per-block descriptors, 0: walks the topology tables (default)

@@ -18,6 +18,7 @@ namespace hb {
 void         cudaCheck( cudaError_t e, const char* what );
 cudaStream_t currentStream();
 int          tuning( const std::string& key, int dflt );
+bool         p2pUsable(); // peer-memory windows connected and not switched off (tuning "p2p")
 // temporarily redirects the library's stream (ghost exchange on the side stream)
 struct StreamScope
 {
@@ -116,6 +117,9 @@ struct hb_function
    void touched( int L ) { mirrorsStale[L - minLevel] = 1; } // call after every write to the level's arena
    bool stale( int L ) const { return st_nranks() > 1 && mirrorsStale[L - minLevel] != 0; }
    int  st_nranks() const;
+   // arguments for nMessages consecutive ghost exchanges of level L over the peer-memory windows (advances the pair counters);
+   // false -- and out.np = 0 -- on one rank or when the windows are not in use
+   bool p2pPrepare( int L, int nMessages, HbP2PArgs& out );
    void syncMirrors( int L );                                // ghost exchange if stale (no-op on one rank)
    double*        arena( int L ) const;
    double* const* ptrs( int L ) const;

@@ -64,6 +64,15 @@ int hb_set_allreduce( hb_allreduce_fn fn, void* ctx );
 int hb_nccl_unique_id( void* id128 );
 int hb_nccl_init( const void* id128, int rank, int n_ranks );
 int hb_nccl_finalize( void );
+/* Peer-memory ghost exchange (one node, NVLink / NVSwitch): on top of the NCCL communicator (still used for reductions),
+ * every rank allocates a window (hb_p2p_window returns its 64-byte CUDA IPC handle; segment_bytes bounds one ghost message
+ * to one neighbour, 16 bytes per double), the host plumbing all-gathers the handles, hb_p2p_connect maps them.  From then on one kernel per
+ * exchange packs into the neighbours' windows, signals, waits and unpacks (no NCCL call on that path).  hb_p2p_active
+ * returns 1 when the path is in use and the number of exchanges it has carried. */
+int hb_p2p_window( void* handle64, long long segment_bytes, int n_ranks );
+int hb_p2p_connect( const void* handles /* n_ranks x 64 bytes, rank order */, int rank, int n_ranks );
+int hb_p2p_finalize( void );
+int hb_p2p_active( long long* exchanges );
 /* Alternative for hosts without NCCL (CPU tests over gloo/MPI): called with the packed send buffers of every neighbouring
  * rank and the receive buffers to fill; buffers live where function data lives (device memory in the product build). */
 typedef int ( *hb_exchange_fn )( void* ctx, int n_peers, const int* peers, double* const* send, const long long* n_send,

@@ -1,5 +1,6 @@
 """Worker of tests/test_gpu_multirank.py: one rank (one GPU) of a world_size-2 NCCL job running the PRODUCT library.
-Checks that the partitioned path (ghost exchange = pack kernel -> ncclSend/ncclRecv -> unpack kernel inside the library)
+Checks that the partitioned path (ghost exchange inside the library: one kernel over peer-memory windows, or with HB_P2P=0
+pack kernel -> ncclSend/ncclRecv -> unpack kernel)
 reproduces the one-rank run on the same mesh bit for bit, and the oracle within 1e-12."""
 import os
 import sys
@@ -75,6 +76,11 @@ def main():
     cells_p, ap_p, so_p, x_p, res_p = run(rank, world)
     calls, sent = comm.exchange_stats(lib)
     assert calls > 0 and sent > 0
+    active, carried = comm.p2p_active(lib)
+    if os.environ.get("HB_P2P", "1") != "0":  # one kernel per exchange over the neighbours' peer-memory windows
+        assert active and carried == calls, (active, carried, calls)
+    else:  # pack kernel -> ncclSend/ncclRecv -> unpack kernel
+        assert not active and carried == 0
     cells_1, ap_1, so_1, x_1, res_1 = run(0, 1)
     n = len(ap_p) // len(cells_p)
     for i, c in enumerate(cells_p):

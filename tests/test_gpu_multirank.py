@@ -1,4 +1,5 @@
-"""Two ranks on two GPUs of one box, NCCL: the partitioned product path against the one-rank run (skipped with < 2 GPUs)."""
+"""Two ranks on two GPUs of one box: the partitioned product path (ghost exchange over peer-memory windows, p2p = 1, or
+NCCL send/recv, p2p = 0) against the one-rank run (skipped with < 2 GPUs)."""
 import os
 import socket
 import subprocess
@@ -10,7 +11,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
 @pytest.mark.gpu
-def test_two_gpus_nccl_ghost_exchange():
+@pytest.mark.parametrize("p2p", ["1", "0"])
+def test_two_gpus_ghost_exchange(p2p):
     import torch
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
@@ -19,7 +21,7 @@ def test_two_gpus_nccl_ghost_exchange():
         port = s.getsockname()[1]
     procs = []
     for r in range(2):
-        env = dict(os.environ, RANK=str(r), LOCAL_RANK=str(r), WORLD_SIZE="2", MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+        env = dict(os.environ, RANK=str(r), LOCAL_RANK=str(r), WORLD_SIZE="2", MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), HB_P2P=p2p)
         procs.append(subprocess.Popen([sys.executable, os.path.join(ROOT, "tests", "multirank_gpu_worker.py")], env=env,
                                       stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True))
     outs = []

@@ -3,12 +3,18 @@ import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 import hyteg_b200 as hb
-from hyteg_b200 import api, meshes
-lib = hb.get_lib(); lib.check(lib.dll.hb_device_init(0))
+from hyteg_b200 import api, comm, meshes
+world, rank, local = int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0))
+torch.cuda.set_device(local)
+lib = hb.get_lib(); lib.check(lib.dll.hb_device_init(local))
+if world > 1:  # torchrun: box of `world` cubes, one per rank (the bench's weak-scaling mesh)
+    import torch.distributed as dist
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    comm.init_nccl(lib)
 s = torch.cuda.current_stream(); lib.dll.hb_set_stream(s.cuda_stream)
-v, c = meshes.cube_6el()
+v, c = meshes.cube_6el() if world == 1 else meshes.cuboid(world, 1, 1, hi=(float(world), 1.0, 1.0))
 LMAX = 8
-st = api.PrimitiveStorage(v, c); st.setMeshBoundaryFlagsOnBoundary(1, 0, True)
+st = api.PrimitiveStorage(v, c, rank, world); st.setMeshBoundaryFlagsOnBoundary(1, 0, True)
 A = api.P1ConstantLaplaceOperator(st, 0, LMAX)
 x, b, r = (api.P1Function(n, st, 0, LMAX) for n in "xbr")
 R, P = api.P1toP1LinearRestriction(), api.P1toP1LinearProlongation()
@@ -28,5 +34,5 @@ for L in range(1, LMAX + 1):
     pr = t(lambda: P.prolongateAndAdd(x, L - 1, hb.SMOOTH_FLAG))
     lvl = 6 * sor + res + rs + pr
     tot += lvl
-    print(f"L{L}: sor {sor:8.1f} us  residual {res:7.1f}  restrict {rs:7.1f}  prolongateAndAdd {pr:7.1f}  | V(3,3) share {lvl:8.1f} us")
-print(f"sum over levels {tot/1e3:.2f} ms (plus CG on level 0)")
+    if rank == 0: print(f"L{L}: sor {sor:8.1f} us  residual {res:7.1f}  restrict {rs:7.1f}  prolongateAndAdd {pr:7.1f}  | V(3,3) share {lvl:8.1f} us")
+if rank == 0: print(f"sum over levels {tot/1e3:.2f} ms (plus CG on level 0)")
