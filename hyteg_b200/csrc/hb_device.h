@@ -214,12 +214,12 @@ __device__ __forceinline__ void hb_boundary_stencil( const HbLevelView&   lv,
 // a copy: the barycentric weights are taken w.r.t. the primitive's macro vertices sorted by global id.
 //   macro vertex: 0 ; macro edge: parity of the position along the edge (2 colours);
 //   macro face: (b1 + 2 b2) mod 3, a proper 3-colouring of the triangular lattice.
-__device__ __forceinline__ int hb_interface_colour_gv( const int32_t* gv, int N, int x, int y, int z );
-__device__ __forceinline__ int hb_interface_colour( const HbCellInfo& ci, int N, int x, int y, int z )
+__host__ __device__ __forceinline__ int hb_interface_colour_gv( const int32_t* gv, int N, int x, int y, int z );
+__host__ __device__ __forceinline__ int hb_interface_colour( const HbCellInfo& ci, int N, int x, int y, int z )
 {
    return hb_interface_colour_gv( ci.gv, N, x, y, z );
 }
-__device__ __forceinline__ int hb_interface_colour_gv( const int32_t* gv, int N, int x, int y, int z )
+__host__ __device__ __forceinline__ int hb_interface_colour_gv( const int32_t* gv, int N, int x, int y, int z )
 {
    const int b[4] = { N - x - y - z, x, y, z };
    int       idx[4];

@@ -95,6 +95,15 @@ struct HbBndPoint
 };
 
 // Per-level geometry/topology tables living in device memory.  Passed to kernels by value.
+// work lists of the single-CTA SOR sweep (small levels): phases 0 macro vertices | 1,2 edge colours | 3,4,5 face colours
+// (i = index into bnd, meshBoundaryFlag of the primitive in bits 24..31) | 6..9 interior colours (i = local array index)
+struct HbPhaseItem
+{
+   int32_t cell;
+   int32_t i;
+};
+#define HB_NPHASE 10
+
 struct HbLevelView
 {
    int32_t level;
@@ -116,6 +125,9 @@ struct HbLevelView
    int32_t             nChunks;
    int32_t             pad0;
    const HbChunkDesc*  descs; // [nCells * nChunks] or null
+   const HbPhaseItem*  phaseItems; // null on levels too large for the single-CTA sweep
+   int32_t             phaseStart[HB_NPHASE + 1];
+   int32_t             pad1;
 };
 
 // BoundaryCondition of a function: meshBoundaryFlag -> DoFType

@@ -527,23 +527,22 @@ __global__ void __launch_bounds__( 1024 ) hb_sor_small_kernel( const HbLevelView
       if ( px.np > 0 )
          hb_p2p_exchange_inline( a.dst, px, m++, [] { __syncthreads(); } );
    };
-   const int       N      = lv.N;
-   const long long nItems = (long long) lv.nCells * lv.nBnd;
-   const long long nAll   = (long long) lv.nCells * lv.cellSize;
+   const int N = lv.N;
+   // the phases walk precomputed work lists (HbLevelView::phaseItems): no per-phase scan of all interface points
    auto interfacePhase = [&]( int dim, int colour ) {
+      const int k  = dim == 0 ? 0 : ( dim == 1 ? 1 + colour : 3 + colour );
+      const int i0 = lv.phaseStart[k], i1 = lv.phaseStart[k + 1];
       for ( int pass = 0; pass < 2; pass++ ) // 0: evaluate into scratch, 1: commit to all local copies
       {
-         for ( long long item = threadIdx.x; item < nItems; item += blockDim.x )
+         for ( int it = i0 + threadIdx.x; it < i1; it += blockDim.x )
          {
-            const int         cell = (int) ( item / lv.nBnd );
-            const int         i    = (int) ( item - (long long) cell * lv.nBnd );
+            const HbPhaseItem q = lv.phaseItems[it];
+            if ( !( ( a.selMask >> ( ( q.i >> 24 ) & 0xff ) ) & 1 ) )
+               continue;
+            const int         cell = q.cell, i = q.i & 0xffffff;
             const HbBndPoint  p    = lv.bnd[i];
             const HbCellInfo* ci   = lv.cells + cell;
-            const HbRegion    reg  = ci->region[p.mask];
-            if ( !( reg.owner & 2 ) || reg.dim != dim || !( ( a.selMask >> reg.bflag ) & 1 ) )
-               continue;
-            if ( hb_interface_colour( *ci, N, p.x, p.y, p.z ) != colour )
-               continue;
+            const size_t      item = (size_t) cell * lv.nBnd + i;
             if ( pass == 0 )
             {
                double sNb, diag;
@@ -568,13 +567,12 @@ __global__ void __launch_bounds__( 1024 ) hb_sor_small_kernel( const HbLevelView
       }
    };
    auto interiorPhase = [&]( int colour ) {
-      for ( long long g = threadIdx.x; g < nAll; g += blockDim.x )
+      for ( int it = lv.phaseStart[6 + colour] + threadIdx.x; it < lv.phaseStart[7 + colour]; it += blockDim.x )
       {
-         const int        cell  = (int) ( g / lv.cellSize );
-         const int        local = (int) ( g - (long long) cell * lv.cellSize );
-         const HbBndPoint q     = lv.xyz[local];
-         if ( q.mask != 0 || ( ( q.x + 2 * q.y + 3 * q.z ) & 3 ) != colour )
-            continue;
+         const HbPhaseItem pi    = lv.phaseItems[it];
+         const int         cell  = pi.cell, local = pi.i;
+         const size_t      g     = (size_t) cell * lv.cellSize + local;
+         const HbBndPoint  q     = lv.xyz[local];
          if ( !( ( a.selMask >> lv.cells[cell].region[0].bflag ) & 1 ) )
             continue;
          const double* w = a.W + (size_t) cell * HB_NMASK * HB_NDIR;
@@ -595,7 +593,7 @@ __global__ void __launch_bounds__( 1024 ) hb_sor_small_kernel( const HbLevelView
          sum += w[D_TW] * S[hb_index( N, x - 1, y, z + 1 )];
          sum += w[D_TS] * S[hb_index( N, x, y - 1, z + 1 )];
          sum += w[D_TSE] * S[hb_index( N, x + 1, y - 1, z + 1 )];
-         hb_epilogue< HB_SOR >( a, a.dst + g, (size_t) g, sum, w[D_C], S[local] );
+         hb_epilogue< HB_SOR >( a, a.dst + g, g, sum, w[D_C], S[local] );
       }
       __syncthreads();
    };
@@ -743,7 +741,7 @@ bool hb_launch_sor_small( const HbLevelView& lv, const HbStencilArgs& a, int bac
 #ifdef HB_EMUL
    return false;
 #else
-   if ( (long long) lv.nCells * lv.cellSize > 16384 )
+   if ( !hb_sor_small_fits( lv ) || !lv.phaseItems )
       return false; // more than 16 strided passes per interior colour: the multi-launch path wins
    hb_sor_small_kernel<<< 1, 1024, 0, st >>>( lv, a, backwards, px );
    return true;

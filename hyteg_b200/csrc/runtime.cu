@@ -87,6 +87,7 @@ void hb_storage::uploadTopologyTables()
    for ( auto& kv : levels )
    {
       buildChunkDescs( *kv.second );
+      buildPhaseItems( *kv.second );
       kv.second->view.cells  = dCells.ptr;
       kv.second->view.copies = dCopies.ptr;
       kv.second->view.regionCopies = dRegionCopies.ptr;
@@ -122,6 +123,46 @@ void hb_storage::buildChunkDescs( hb::LevelTables& lt )
       }
    lt.descs.upload( d );
    lt.view.descs = lt.descs.ptr;
+}
+
+void hb_storage::buildPhaseItems( hb::LevelTables& lt )
+{
+   HbLevelView& v = lt.view;
+   v.phaseItems   = nullptr;
+   for ( int k = 0; k <= HB_NPHASE; k++ )
+      v.phaseStart[k] = 0;
+   if ( !hb_sor_small_fits( v ) )
+      return;
+   std::vector< std::vector< HbPhaseItem > > lists( HB_NPHASE );
+   for ( int c = 0; c < view.nLocal; c++ )
+   {
+      const HbCellInfo& ci = view.cells[c];
+      for ( size_t i = 0; i < lt.hBnd.size(); i++ )
+      {
+         const HbBndPoint& p   = lt.hBnd[i];
+         const HbRegion&   reg = ci.region[p.mask];
+         if ( !( reg.owner & 2 ) )
+            continue; // another macro-cell of this rank evaluates the point
+         const int colour = hb_interface_colour( ci, v.N, p.x, p.y, p.z );
+         const int k      = reg.dim == 0 ? 0 : ( reg.dim == 1 ? 1 + colour : 3 + colour );
+         lists[k].push_back( HbPhaseItem{ c, (int32_t) i | ( (int32_t) reg.bflag << 24 ) } );
+      }
+      for ( size_t l = 0; l < lt.hXyz.size(); l++ )
+      {
+         const HbBndPoint& q = lt.hXyz[l];
+         if ( q.mask == 0 )
+            lists[6 + ( ( q.x + 2 * q.y + 3 * q.z ) & 3 )].push_back( HbPhaseItem{ c, (int32_t) l } );
+      }
+   }
+   std::vector< HbPhaseItem > all;
+   for ( int k = 0; k < HB_NPHASE; k++ )
+   {
+      v.phaseStart[k] = (int32_t) all.size();
+      all.insert( all.end(), lists[k].begin(), lists[k].end() );
+   }
+   v.phaseStart[HB_NPHASE] = (int32_t) all.size();
+   lt.phaseItems.upload( all );
+   v.phaseItems = lt.phaseItems.ptr;
 }
 
 hb::LevelTables& hb_storage::level( int L )
@@ -184,6 +225,7 @@ hb::LevelTables& hb_storage::level( int L )
    }
    lt->chunks.upload( chunks );
    lt->hChunks = chunks;
+   lt->hBnd    = bnd;
    lt->bnd.upload( bnd );
    lt->xyz.upload( lt->hXyz );
    lt->mask.upload( mask );
@@ -215,6 +257,7 @@ hb::LevelTables& hb_storage::level( int L )
    v.chunks       = lt->chunks.ptr;
    v.nChunks      = (int) chunks.size();
    buildChunkDescs( *lt );
+   buildPhaseItems( *lt );
    auto& ref      = *lt;
    levels[L]      = std::move( lt );
    return ref;

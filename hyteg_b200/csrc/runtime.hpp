@@ -65,6 +65,8 @@ struct LevelTables
    DeviceBuffer< HbTile >     tiles;
    DeviceBuffer< HbBndChunk > chunks;
    std::vector< HbBndChunk >  hChunks;
+   std::vector< HbBndPoint >  hBnd;
+   DeviceBuffer< HbPhaseItem > phaseItems; // work lists of the single-CTA SOR sweep, rebuilt with the topology tables
    DeviceBuffer< HbChunkDesc > descs; // per (local macro-cell, chunk), rebuilt with the topology tables
    DeviceBuffer< HbItem >     items;   // work items of the TMA-streamed interior kernel
    DeviceBuffer< HbItem >     itemsShuffle; // work items of the centre-column + shuffle interior kernel
@@ -102,6 +104,7 @@ struct hb_storage
    hb::LevelTables& level( int L );
    hb::LevelTables::Exchange& exchange( int L );
    void             buildChunkDescs( hb::LevelTables& lt ); // builds the level's exchange tables on first use
+   void             buildPhaseItems( hb::LevelTables& lt );
    void             uploadTopologyTables();
    ~hb_storage();
 };

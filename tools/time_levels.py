@@ -11,6 +11,8 @@ if world > 1:  # torchrun: box of `world` cubes, one per rank (the bench's weak-
     import torch.distributed as dist
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     comm.init_nccl(lib)
+for kv in filter(None, os.environ.get("HB_TUNING", "").split(",")):
+    k, val = kv.split("="); lib.dll.hb_set_tuning(k.encode(), int(val))
 s = torch.cuda.current_stream(); lib.dll.hb_set_stream(s.cuda_stream)
 v, c = meshes.cube_6el() if world == 1 else meshes.cuboid(world, 1, 1, hi=(float(world), 1.0, 1.0))
 LMAX = 8
