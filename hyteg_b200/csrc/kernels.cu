@@ -468,8 +468,7 @@ __device__ __forceinline__ void hb_p2p_exchange_inline( double* arena, const HbP
    hb_p2p_wait_slot( p, m );
    hb_p2p_put( arena, p.sendOff, p, m, t0, stride );
    hb_p2p_get( arena, p.recvOff, p, m, t0, stride );
-   __threadfence();
-   bar();
+   bar(); // (no __threadfence() here: it would wait for this thread's NVLink puts to be acknowledged; the barrier orders the arena writes)
    if ( blockIdx.x == 0 )
       hb_p2p_ack( p, m );
 }
@@ -598,6 +597,8 @@ __global__ void __launch_bounds__( 1024 ) hb_sor_small_kernel( const HbLevelView
       __syncthreads();
    };
    const int nColours[3] = { 1, 2, 3 };
+   if ( px.syncFirst )
+      exchange();
    if ( !backwards )
    {
       for ( int d = 0; d <= 2; d++ )

@@ -42,6 +42,7 @@ struct alignas( 16 ) HbP2PLine
 struct HbP2PArgs
 {
    int32_t             np;
+   int32_t             syncFirst; // fused sweeps: exchange once before the first phase (the mirrored layers were stale)
    long long           sendStart[HB_P2P_MAXPEERS + 1], recvStart[HB_P2P_MAXPEERS + 1];
    const long long*    sendOff;                     // arena offsets of the layers that travel / that arrive (Exchange tables)
    const long long*    recvOff;
