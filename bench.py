@@ -186,7 +186,8 @@ def main():
     from hyteg_b200 import comm
     if world > 1:
         # weak scaling: a box of `world` unit cubes (6 macro-tets each), macro-cells partitioned in contiguous blocks so that
-        # every rank owns one cube; the ghost layers on the faces between the cubes travel over NCCL (NVLink) inside the step
+        # every rank owns one cube; the ghost layers on the faces between the cubes travel over NVLink inside the step: remote
+        # stores into the neighbours' peer-memory windows (HB_P2P=0: pack -> ncclSend/ncclRecv -> unpack)
         v, c = meshes.cuboid(world, 1, 1, hi=(float(world), 1.0, 1.0))
         comm.init_nccl(lib)
     else:
@@ -294,14 +295,15 @@ def main():
         achieved = BYTES_PER_DOF["apply"] * n_interior / (ms_interior * 1e-3) / 1e9
         whole = BYTES_PER_DOF["apply"] * ndof_rank / (ms_apply * 1e-3) / 1e9
         npeers, nsend, nrecv = st.exchange_info(L)
+        xmode = "NVLink peer-memory windows, one kernel per exchange" if (world > 1 and comm.p2p_active(lib)[0]) else "NCCL send/recv"
         line = {"metric": "P1 constant-stencil apply throughput", "value": gd(ms_apply), "unit": "GDoF/s", "n_gpus": world,
                 "steps": args.steps, "warmup": W, "ms_per_step": ms_apply, "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "f64", "data": "synthetic",
                 "config": {"workload": f"cube_6el level {L} P1 Laplace constant-stencil apply, {int(ndof_rank)} DoFs per GPU" if world == 1 else
                            f"box of {world} cubes (6 macro-tets each) level {L}, partitioned one cube per GPU, {int(ndof_rank)} DoFs per GPU, "
-                           f"ghost exchange of {8 * nsend} B with {npeers} neighbour rank(s) inside every step (NCCL send/recv)",
+                           f"ghost exchange of {8 * nsend} B with {npeers} neighbour rank(s) inside every step ({xmode})",
                            "l2": "src+dst arrays %.0f MB > 126 MB L2" % (2 * 8 * n_arr / 1e6),
-                           "multi_gpu": "macro-cells partitioned, ghost layers over NCCL" if world > 1 else "single"},
+                           "multi_gpu": f"macro-cells partitioned, ghost layers over {xmode}" if world > 1 else "single"},
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                              "traffic": NCU_TRAFFIC_INTERIOR_L8 if L == 8 else None, "peak_source": which,
                              "kernel": "hb_shuffle_kernel<APPLY_REPLACE,4,128> (interior points of all local macro-cells, one launch)",
