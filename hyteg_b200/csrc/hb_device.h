@@ -144,22 +144,21 @@ __host__ __device__ __forceinline__ int hb_copy_index( int N, const HbRegionCopy
 // (reference P1Elements.hpp:465-515); the sum over the neighbouring cells is how HyTeG builds its macro-face/edge/vertex
 // stencils (reference P1Elements.hpp:626-720, 870-1017).  All threads of a block work on the same (cell, region), so the
 // region-copy entries, their weights and the valid-direction masks are block-uniform.
-__device__ __forceinline__ void hb_boundary_stencil( const HbLevelView&   lv,
-                                                     const double*        W,
-                                                     const double* const* src,
-                                                     const double*        srcBase,
-                                                     const HbCellInfo*    ci,
-                                                     int                  mask,
-                                                     int                  x,
-                                                     int                  y,
-                                                     int                  z,
-                                                     double&              sNb,
-                                                     double&              diag )
+__device__ __forceinline__ void hb_boundary_stencil_range( const HbLevelView&   lv,
+                                                           const double*        W,
+                                                           const double* const* src,
+                                                           const double*        srcBase,
+                                                           int                  e0,
+                                                           int                  e1,
+                                                           int                  x,
+                                                           int                  y,
+                                                           int                  z,
+                                                           double&              sNb,
+                                                           double&              diag )
 {
    const int N = lv.N;
    sNb         = 0.0;
    diag        = 0.0;
-   const int e0 = ci->rcBegin[mask], e1 = ci->rcBegin[mask + 1];
    for ( int e = e0; e < e1; e++ )
    {
       const HbRegionCopy rc = lv.regionCopies[e];
@@ -208,6 +207,21 @@ __device__ __forceinline__ void hb_boundary_stencil( const HbLevelView&   lv,
       sNb += part;
       diag += w[0];
    }
+}
+
+__device__ __forceinline__ void hb_boundary_stencil( const HbLevelView&   lv,
+                                                     const double*        W,
+                                                     const double* const* src,
+                                                     const double*        srcBase,
+                                                     const HbCellInfo*    ci,
+                                                     int                  mask,
+                                                     int                  x,
+                                                     int                  y,
+                                                     int                  z,
+                                                     double&              sNb,
+                                                     double&              diag )
+{
+   hb_boundary_stencil_range( lv, W, src, srcBase, ci->rcBegin[mask], ci->rcBegin[mask + 1], x, y, z, sNb, diag );
 }
 
 // Colour of an interface point inside its macro primitive, identical in every macro-cell that holds

@@ -103,6 +103,17 @@ struct HbPhaseItem
    int32_t i;
 };
 #define HB_NPHASE 10
+// work lists of the cooperative SOR interface launch: everything a thread needs to start on its point in ONE load (the table walk
+// chunk -> region -> point -> colour -> copy range is five dependent L2 round trips per phase, and a grid barrier empties L1).
+// Phases 0 | 1,2 always; the face phases 3,4,5 only on levels whose six phases run cooperatively (N <= 128).
+struct HbIfaceItem
+{
+   int32_t  cell;
+   int32_t  rc0, rc1; // range in regionCopies: the macro-cells containing the point
+   uint16_t x, y, z;
+   uint8_t  bflag;
+   uint8_t  pad;
+};
 
 struct HbLevelView
 {
@@ -125,6 +136,9 @@ struct HbLevelView
    int32_t             nChunks;
    int32_t             pad0;
    const HbChunkDesc*  descs; // [nCells * nChunks] or null
+   const HbIfaceItem*  ifaceItems;
+   int32_t             ifaceStart[7]; // phase k: [ifaceStart[k], ifaceStart[k+1]); ifaceFaces = 0: phases 3..5 are not listed
+   int32_t             ifaceFaces;
    const HbPhaseItem*  phaseItems; // null on levels too large for the single-CTA sweep
    int32_t             phaseStart[HB_NPHASE + 1];
    int32_t             pad1;

@@ -671,11 +671,46 @@ __global__ void __launch_bounds__( HB_BLOCK, 4 )
       const int dim = k == 0 ? 0 : ( k <= 2 ? 1 : 2 );
       a.dimSel      = 1 << dim;
       a.bndColour   = k == 0 ? 0 : ( k <= 2 ? k - 1 : k - 3 );
-      for ( int blk = blockIdx.x; blk < nBlk; blk += gridDim.x )
-         hb_boundary_block< HB_SOR >( lv, a, blk );
-      grid.sync();
-      for ( int blk = blockIdx.x; blk < nBlk; blk += gridDim.x )
-         hb_commit_block( lv, a, blk );
+      if ( lv.ifaceItems && ( k <= 2 || lv.ifaceFaces ) )
+      {
+         // list form: one load tells a thread its point, the macro-cells containing it and the primitive's boundary flag
+         const int i0 = lv.ifaceStart[k], i1 = lv.ifaceStart[k + 1];
+         const int t0 = i0 + blockIdx.x * blockDim.x + threadIdx.x, stride = gridDim.x * blockDim.x;
+         for ( int it = t0; it < i1; it += stride )
+         {
+            const HbIfaceItem q = lv.ifaceItems[it];
+            if ( !( ( a.selMask >> q.bflag ) & 1 ) )
+               continue;
+            double sNb, diag;
+            hb_boundary_stencil_range( lv, a.W, a.src, a.srcBase, q.rc0, q.rc1, q.x, q.y, q.z, sNb, diag );
+            const size_t gi = (size_t) q.cell * lv.cellSize + (size_t) hb_index( lv.N, q.x, q.y, q.z );
+            double       val;
+            hb_epilogue< HB_SOR >( a, &val, gi, sNb, diag, a.srcBase[gi] );
+            a.scratch[it] = val;
+         }
+         grid.sync();
+         for ( int it = t0; it < i1; it += stride )
+         {
+            const HbIfaceItem q = lv.ifaceItems[it];
+            if ( !( ( a.selMask >> q.bflag ) & 1 ) )
+               continue;
+            const double val = a.scratch[it];
+            for ( int e = q.rc0; e < q.rc1; e++ )
+            {
+               const HbRegionCopy rc = lv.regionCopies[e];
+               if ( rc.slot < lv.nCells )
+                  a.dst[(size_t) rc.slot * lv.cellSize + (size_t) hb_copy_index( lv.N, rc, q.x, q.y, q.z )] = val;
+            }
+         }
+      }
+      else
+      {
+         for ( int blk = blockIdx.x; blk < nBlk; blk += gridDim.x )
+            hb_boundary_block< HB_SOR >( lv, a, blk );
+         grid.sync();
+         for ( int blk = blockIdx.x; blk < nBlk; blk += gridDim.x )
+            hb_commit_block( lv, a, blk );
+      }
       if ( px.np > 0 && k != ( backwards ? 0 : 5 ) )
          hb_p2p_exchange_inline( a.dst, px, m++, [&] { grid.sync(); } ); // starts and ends with a grid barrier
       else
@@ -714,7 +749,7 @@ bool hb_launch_sor_interface_coop( const HbLevelView& lv, const HbStencilArgs& a
       return false;
    const int nSm = hb_coop_sms, perSm = hb_coop_per_sm;
    const int nBlk = lv.nCells * lv.nChunks;
-   int       grid = nSm * perSm;
+   int       grid = nSm * ( hb_coop_ctas_per_sm > 0 && hb_coop_ctas_per_sm < perSm ? hb_coop_ctas_per_sm : perSm );
    if ( grid > nBlk )
       grid = nBlk;
    if ( grid < 1 )
@@ -753,6 +788,7 @@ bool hb_launch_sor_small( const HbLevelView& lv, const HbStencilArgs& a, int bac
 // table walk -- the kernel is bound by the L1 wavefronts of its scattered gathers, not by its dependent look-ups -- so the
 // table walk (4 CTAs/SM) stays the default.
 int hb_use_desc = 0;
+int hb_coop_ctas_per_sm = 0; // A/B knob "sor_coop_ctas": CTAs per SM of the cooperative SOR launch (0: as many as fit)
 
 template < int MODE >
 static void hb_launch_stencil_mode( const HbLevelView& lv, const HbStencilArgs& a, bool interior, bool boundary, cudaStream_t st )

@@ -63,4 +63,5 @@ bool hb_launch_sor_small( const HbLevelView& lv, const HbStencilArgs& a, int bac
 // launch; false if unavailable
 bool hb_sor_coop_available();
 bool hb_launch_sor_interface_coop( const HbLevelView& lv, const HbStencilArgs& a, int backwards, int kLo, int kHi, const HbP2PArgs& px, cudaStream_t st );
+extern int hb_coop_ctas_per_sm; // cooperative SOR launch: CTAs per SM (0: as many as fit)
 extern int hb_use_desc; // 1: interface kernel reads per-block descriptors, 0: walks the topology tables (default)

@@ -128,6 +128,44 @@ void hb_storage::buildChunkDescs( hb::LevelTables& lt )
 void hb_storage::buildPhaseItems( hb::LevelTables& lt )
 {
    HbLevelView& v = lt.view;
+   {
+      // cooperative interface launch: per-phase lists of the points this rank evaluates (rank-local owners)
+      static_assert( sizeof( HbIfaceItem ) == 20, "HbIfaceItem layout" );
+      v.ifaceFaces = v.N <= 128 ? 1 : 0;
+      std::vector< std::vector< HbIfaceItem > > lists( 6 );
+      for ( int c = 0; c < view.nLocal; c++ )
+      {
+         const HbCellInfo& ci = view.cells[c];
+         for ( const HbBndPoint& p : lt.hBnd )
+         {
+            const HbRegion& reg = ci.region[p.mask];
+            if ( !( reg.owner & 2 ) || ( reg.dim == 2 && !v.ifaceFaces ) )
+               continue;
+            const int   colour = hb_interface_colour( ci, v.N, p.x, p.y, p.z );
+            const int   k      = reg.dim == 0 ? 0 : ( reg.dim == 1 ? 1 + colour : 3 + colour );
+            HbIfaceItem q{};
+            q.cell  = c;
+            q.rc0   = ci.rcBegin[p.mask];
+            q.rc1   = ci.rcBegin[p.mask + 1];
+            q.x     = p.x;
+            q.y     = p.y;
+            q.z     = p.z;
+            q.bflag = (uint8_t) reg.bflag;
+            lists[k].push_back( q );
+         }
+      }
+      std::vector< HbIfaceItem > all;
+      for ( int k = 0; k < 6; k++ )
+      {
+         v.ifaceStart[k] = (int32_t) all.size();
+         all.insert( all.end(), lists[k].begin(), lists[k].end() );
+      }
+      v.ifaceStart[6] = (int32_t) all.size();
+      lt.ifaceItems.upload( all );
+      v.ifaceItems = lt.ifaceItems.ptr;
+      if ( lt.scratch.n < all.size() )
+         lt.scratch.alloc( all.size() );
+   }
    v.phaseItems   = nullptr;
    for ( int k = 0; k <= HB_NPHASE; k++ )
       v.phaseStart[k] = 0;
@@ -384,6 +422,8 @@ int hb_set_tuning( const char* key, int value )
 {
    if ( std::string( key ) == "iface_desc" )
       hb_use_desc = ( value == -2147483647 - 1 ) ? 0 : value;
+   if ( std::string( key ) == "sor_coop_ctas" )
+      hb_coop_ctas_per_sm = ( value == -2147483647 - 1 ) ? 0 : value;
    if ( value == -2147483647 - 1 ) // INT_MIN: back to the built-in default
       hb::g_tuning.erase( key );
    else

@@ -66,6 +66,7 @@ struct LevelTables
    DeviceBuffer< HbBndChunk > chunks;
    std::vector< HbBndChunk >  hChunks;
    std::vector< HbBndPoint >  hBnd;
+   DeviceBuffer< HbIfaceItem > ifaceItems; // work lists of the cooperative SOR interface launch
    DeviceBuffer< HbPhaseItem > phaseItems; // work lists of the single-CTA SOR sweep, rebuilt with the topology tables
    DeviceBuffer< HbChunkDesc > descs; // per (local macro-cell, chunk), rebuilt with the topology tables
    DeviceBuffer< HbItem >     items;   // work items of the TMA-streamed interior kernel
