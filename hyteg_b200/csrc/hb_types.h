@@ -95,12 +95,14 @@ struct HbBndPoint
 };
 
 // Per-level geometry/topology tables living in device memory.  Passed to kernels by value.
-// work lists of the single-CTA SOR sweep (small levels): phases 0 macro vertices | 1,2 edge colours | 3,4,5 face colours
-// (i = index into bnd, meshBoundaryFlag of the primitive in bits 24..31) | 6..9 interior colours (i = local array index)
+// interior work lists of the single-CTA SOR sweep (small levels): phases 6..9 = interior colours (i = local array index);
+// the interface phases 0..5 use the HbIfaceItem lists below
 struct HbPhaseItem
 {
-   int32_t cell;
-   int32_t i;
+   int32_t  cell;
+   uint16_t x, y, z;
+   uint8_t  bflag; // meshBoundaryFlag of the macro-cell
+   uint8_t  pad;
 };
 #define HB_NPHASE 10
 // work lists of the cooperative SOR interface launch: everything a thread needs to start on its point in ONE load (the table walk

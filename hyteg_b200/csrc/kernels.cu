@@ -527,38 +527,34 @@ __global__ void __launch_bounds__( 1024 ) hb_sor_small_kernel( const HbLevelView
          hb_p2p_exchange_inline( a.dst, px, m++, [] { __syncthreads(); } );
    };
    const int N = lv.N;
-   // the phases walk precomputed work lists (HbLevelView::phaseItems): no per-phase scan of all interface points
+   // the phases walk precomputed work lists (HbLevelView::ifaceItems / phaseItems): no per-phase scan of all interface points
    auto interfacePhase = [&]( int dim, int colour ) {
       const int k  = dim == 0 ? 0 : ( dim == 1 ? 1 + colour : 3 + colour );
-      const int i0 = lv.phaseStart[k], i1 = lv.phaseStart[k + 1];
+      const int i0 = lv.ifaceStart[k], i1 = lv.ifaceStart[k + 1];
       for ( int pass = 0; pass < 2; pass++ ) // 0: evaluate into scratch, 1: commit to all local copies
       {
          for ( int it = i0 + threadIdx.x; it < i1; it += blockDim.x )
          {
-            const HbPhaseItem q = lv.phaseItems[it];
-            if ( !( ( a.selMask >> ( ( q.i >> 24 ) & 0xff ) ) & 1 ) )
+            const HbIfaceItem q = lv.ifaceItems[it];
+            if ( !( ( a.selMask >> q.bflag ) & 1 ) )
                continue;
-            const int         cell = q.cell, i = q.i & 0xffffff;
-            const HbBndPoint  p    = lv.bnd[i];
-            const HbCellInfo* ci   = lv.cells + cell;
-            const size_t      item = (size_t) cell * lv.nBnd + i;
             if ( pass == 0 )
             {
                double sNb, diag;
-               hb_boundary_stencil( lv, a.W, a.src, a.srcBase, ci, p.mask, p.x, p.y, p.z, sNb, diag );
-               const size_t gi = (size_t) cell * lv.cellSize + (size_t) hb_index( N, p.x, p.y, p.z );
+               hb_boundary_stencil_range( lv, a.W, a.src, a.srcBase, q.rc0, q.rc1, q.x, q.y, q.z, sNb, diag );
+               const size_t gi = (size_t) q.cell * lv.cellSize + (size_t) hb_index( N, q.x, q.y, q.z );
                double       val;
                hb_epilogue< HB_SOR >( a, &val, gi, sNb, diag, a.srcBase[gi] );
-               a.scratch[item] = val;
+               a.scratch[it] = val;
             }
             else
             {
-               const double val = a.scratch[item];
-               for ( int e = ci->rcBegin[p.mask]; e < ci->rcBegin[p.mask + 1]; e++ )
+               const double val = a.scratch[it];
+               for ( int e = q.rc0; e < q.rc1; e++ )
                {
                   const HbRegionCopy rc = lv.regionCopies[e];
                   if ( rc.slot < lv.nCells )
-                     a.dst[(size_t) rc.slot * lv.cellSize + (size_t) hb_copy_index( N, rc, p.x, p.y, p.z )] = val;
+                     a.dst[(size_t) rc.slot * lv.cellSize + (size_t) hb_copy_index( N, rc, q.x, q.y, q.z )] = val;
                }
             }
          }
@@ -568,15 +564,13 @@ __global__ void __launch_bounds__( 1024 ) hb_sor_small_kernel( const HbLevelView
    auto interiorPhase = [&]( int colour ) {
       for ( int it = lv.phaseStart[6 + colour] + threadIdx.x; it < lv.phaseStart[7 + colour]; it += blockDim.x )
       {
-         const HbPhaseItem pi    = lv.phaseItems[it];
-         const int         cell  = pi.cell, local = pi.i;
-         const size_t      g     = (size_t) cell * lv.cellSize + local;
-         const HbBndPoint  q     = lv.xyz[local];
-         if ( !( ( a.selMask >> lv.cells[cell].region[0].bflag ) & 1 ) )
+         const HbPhaseItem q = lv.phaseItems[it];
+         if ( !( ( a.selMask >> q.bflag ) & 1 ) )
             continue;
-         const double* w = a.W + (size_t) cell * HB_NMASK * HB_NDIR;
-         const double* S = a.srcBase + (size_t) cell * lv.cellSize;
-         const int     x = q.x, y = q.y, z = q.z;
+         const int     cell = q.cell, x = q.x, y = q.y, z = q.z, local = hb_index( N, x, y, z );
+         const size_t  g    = (size_t) cell * lv.cellSize + local;
+         const double* w    = a.W + (size_t) cell * HB_NMASK * HB_NDIR;
+         const double* S    = a.srcBase + (size_t) cell * lv.cellSize;
          // same summation order as hb_interior_tile
          double sum = w[D_W] * S[hb_index( N, x - 1, y, z )];
          sum += w[D_E] * S[hb_index( N, x + 1, y, z )];
@@ -777,7 +771,7 @@ bool hb_launch_sor_small( const HbLevelView& lv, const HbStencilArgs& a, int bac
 #ifdef HB_EMUL
    return false;
 #else
-   if ( !hb_sor_small_fits( lv ) || !lv.phaseItems )
+   if ( !hb_sor_small_fits( lv ) || !lv.phaseItems || !lv.ifaceItems || !lv.ifaceFaces )
       return false; // more than 16 strided passes per interior colour: the multi-launch path wins
    hb_sor_small_kernel<<< 1, 1024, 0, st >>>( lv, a, backwards, px );
    return true;

@@ -174,22 +174,11 @@ void hb_storage::buildPhaseItems( hb::LevelTables& lt )
    std::vector< std::vector< HbPhaseItem > > lists( HB_NPHASE );
    for ( int c = 0; c < view.nLocal; c++ )
    {
-      const HbCellInfo& ci = view.cells[c];
-      for ( size_t i = 0; i < lt.hBnd.size(); i++ )
-      {
-         const HbBndPoint& p   = lt.hBnd[i];
-         const HbRegion&   reg = ci.region[p.mask];
-         if ( !( reg.owner & 2 ) )
-            continue; // another macro-cell of this rank evaluates the point
-         const int colour = hb_interface_colour( ci, v.N, p.x, p.y, p.z );
-         const int k      = reg.dim == 0 ? 0 : ( reg.dim == 1 ? 1 + colour : 3 + colour );
-         lists[k].push_back( HbPhaseItem{ c, (int32_t) i | ( (int32_t) reg.bflag << 24 ) } );
-      }
       for ( size_t l = 0; l < lt.hXyz.size(); l++ )
       {
          const HbBndPoint& q = lt.hXyz[l];
          if ( q.mask == 0 )
-            lists[6 + ( ( q.x + 2 * q.y + 3 * q.z ) & 3 )].push_back( HbPhaseItem{ c, (int32_t) l } );
+            lists[6 + ( ( q.x + 2 * q.y + 3 * q.z ) & 3 )].push_back( HbPhaseItem{ c, q.x, q.y, q.z, (uint8_t) view.cells[c].region[0].bflag, 0 } );
       }
    }
    std::vector< HbPhaseItem > all;
