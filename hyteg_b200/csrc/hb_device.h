@@ -224,6 +224,13 @@ __device__ __forceinline__ void hb_boundary_stencil( const HbLevelView&   lv,
    hb_boundary_stencil_range( lv, W, src, srcBase, ci->rcBegin[mask], ci->rcBegin[mask + 1], x, y, z, sNb, diag );
 }
 
+// SOR update from the full row sum Ax (centre term included), written with explicit fma so that every kernel that uses it rounds
+// the same way:  (1 - omega) c + omega ( invd ( rhs - Ax ) + c )
+__host__ __device__ __forceinline__ double hb_sor_value( double omega, double Ax, double invd, double centre, double rhs )
+{
+   return fma( omega, fma( invd, rhs - Ax, centre ), ( 1.0 - omega ) * centre );
+}
+
 // Colour of an interface point inside its macro primitive, identical in every macro-cell that holds
 // a copy: the barycentric weights are taken w.r.t. the primitive's macro vertices sorted by global id.
 //   macro vertex: 0 ; macro edge: parity of the position along the edge (2 colours);

@@ -650,13 +650,64 @@ __device__ __forceinline__ void hb_commit_block( const HbLevelView& lv, const Hb
    }
 }
 
+// One interior point of an SOR colour pass in the association order of the shuffle kernel (left column, centre column seeded
+// with it, right column added last; shuffle_kernel.cu) -- bit-identical to it, so that a level may run its interior colours
+// through either kernel.
+__device__ __forceinline__ void hb_sor_interior_point( const HbLevelView& lv, const HbStencilArgs& a, const HbPhaseItem q )
+{
+   if ( !( ( a.selMask >> q.bflag ) & 1 ) )
+      return;
+   const int     N = lv.N, x = q.x, y = q.y, z = q.z;
+   const double* w = a.W + (size_t) q.cell * HB_NMASK * HB_NDIR;
+   const double* S = a.srcBase + (size_t) q.cell * lv.cellSize;
+   auto          V = [&]( int dx, int dy, int dz ) { return S[hb_index( N, x + dx, y + dy, z + dz )]; };
+   double l = w[D_W] * V( -1, 0, 0 );
+   l        = fma( w[D_NW], V( -1, 1, 0 ), l );
+   l        = fma( w[D_BNW], V( -1, 1, -1 ), l );
+   l        = fma( w[D_TW], V( -1, 0, 1 ), l );
+   const double centre = V( 0, 0, 0 );
+   double       c      = fma( w[D_C], centre, l );
+   c                   = fma( w[D_N], V( 0, 1, 0 ), c );
+   c                   = fma( w[D_S], V( 0, -1, 0 ), c );
+   c                   = fma( w[D_BC], V( 0, 0, -1 ), c );
+   c                   = fma( w[D_BN], V( 0, 1, -1 ), c );
+   c                   = fma( w[D_TC], V( 0, 0, 1 ), c );
+   c                   = fma( w[D_TS], V( 0, -1, 1 ), c );
+   double r = w[D_E] * V( 1, 0, 0 );
+   r        = fma( w[D_SE], V( 1, -1, 0 ), r );
+   r        = fma( w[D_BE], V( 1, 0, -1 ), r );
+   r        = fma( w[D_TSE], V( 1, -1, 1 ), r );
+   const size_t g = (size_t) q.cell * lv.cellSize + (size_t) hb_index( N, x, y, z );
+   a.dst[g]       = hb_sor_value( a.omega, c + r, 1.0 / w[D_C], centre, a.rhs[g] );
+}
+
 __global__ void __launch_bounds__( HB_BLOCK, 4 )
-    hb_sor_interface_coop_kernel( const HbLevelView lv, HbStencilArgs a, const int backwards, const int kLo, const int kHi, const HbP2PArgs px )
+    hb_sor_interface_coop_kernel( const HbLevelView lv, HbStencilArgs a, const int backwards, const int kLo, const int kHi, const HbP2PArgs px,
+                                  const int interior )
 {
    cooperative_groups::grid_group grid = cooperative_groups::this_grid();
    unsigned                       m    = 0; // more than one rank (px.np > 0): ghost exchange after every phase but the sweep's last
    const int nBlk = lv.nCells * lv.nChunks;
    a.toScratch    = 1;
+   // interior != 0 (levels with interior work lists, N <= 64): the four interior colours run in here as well -- the whole sweep
+   // is one launch.  Forward: after the interface phases; backward: before them, followed by a ghost exchange.
+   auto interiorColours = [&]() {
+      const int t0 = blockIdx.x * blockDim.x + threadIdx.x, stride = gridDim.x * blockDim.x;
+      for ( int cc = 0; cc < 4; cc++ )
+      {
+         const int c = backwards ? 3 - cc : cc;
+         for ( int it = lv.phaseStart[6 + c] + t0; it < lv.phaseStart[7 + c]; it += stride )
+            hb_sor_interior_point( lv, a, lv.phaseItems[it] );
+         if ( cc < 3 || backwards )
+            grid.sync();
+      }
+   };
+   if ( interior && backwards )
+   {
+      interiorColours();
+      if ( px.np > 0 )
+         hb_p2p_exchange_inline( a.dst, px, m++, [&] { grid.sync(); } );
+   }
    for ( int ph = 0; ph < 6; ph++ )
    {
       const int k   = backwards ? 5 - ph : ph;          // phases 0: vertices | 1,2: edges | 3,4,5: faces
@@ -710,6 +761,8 @@ __global__ void __launch_bounds__( HB_BLOCK, 4 )
       else
          grid.sync();
    }
+   if ( interior && !backwards )
+      interiorColours();
 }
 #endif
 
@@ -734,7 +787,7 @@ bool hb_sor_coop_available()
 #endif
 }
 
-bool hb_launch_sor_interface_coop( const HbLevelView& lv, const HbStencilArgs& a, int backwards, int kLo, int kHi, const HbP2PArgs& px, cudaStream_t st )
+bool hb_launch_sor_interface_coop( const HbLevelView& lv, const HbStencilArgs& a, int backwards, int kLo, int kHi, const HbP2PArgs& px, int interior, cudaStream_t st )
 {
 #ifdef HB_EMUL
    return false;
@@ -752,7 +805,7 @@ bool hb_launch_sor_interface_coop( const HbLevelView& lv, const HbStencilArgs& a
    HbStencilArgs ac  = a;
    int           bw  = backwards;
    HbP2PArgs     pxc = px;
-   void*         args[] = { &lvc, &ac, &bw, &kLo, &kHi, &pxc };
+   void*         args[] = { &lvc, &ac, &bw, &kLo, &kHi, &pxc, &interior };
    return cudaLaunchCooperativeKernel( (void*) hb_sor_interface_coop_kernel, dim3( grid ), dim3( HB_BLOCK ), args, 0, st ) == cudaSuccess;
 #endif
 }

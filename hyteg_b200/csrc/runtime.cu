@@ -169,8 +169,8 @@ void hb_storage::buildPhaseItems( hb::LevelTables& lt )
    v.phaseItems   = nullptr;
    for ( int k = 0; k <= HB_NPHASE; k++ )
       v.phaseStart[k] = 0;
-   if ( !hb_sor_small_fits( v ) )
-      return;
+   if ( !hb_sor_small_fits( v ) && v.N > 64 )
+      return; // interior lists: single-CTA sweep (small levels) and whole-sweep cooperative launch (N <= 64)
    std::vector< std::vector< HbPhaseItem > > lists( HB_NPHASE );
    for ( int c = 0; c < view.nLocal; c++ )
    {

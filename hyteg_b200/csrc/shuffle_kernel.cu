@@ -76,7 +76,7 @@ __device__ __forceinline__ double epilogue( const HbStencilArgs& a, double Ax, d
    if ( MODE == HB_CHEB_FIRST )
       return invd * ( e - Ax );
    if ( MODE == HB_SOR ) // e = rhs; Ax includes the centre term: invd * ( rhs - sum over neighbours ) = invd * ( e - Ax ) + centre
-      return ( 1.0 - a.omega ) * centre + a.omega * ( invd * ( e - Ax ) + centre );
+      return hb_sor_value( a.omega, Ax, invd, centre, e );
    if ( MODE == HB_CHEB_STEP ) // second store ( aux = e + omega * centre ) is issued by the caller
       return invd * Ax;
    return Ax; // HB_APPLY_REPLACE
