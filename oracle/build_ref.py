@@ -1,0 +1,105 @@
+#!/usr/bin/env python3
+"""TEST INFRASTRUCTURE ONLY — builds the REFERENCE (HyTeG) itself into oracle/_ref/.
+
+Compiles the reference's own source files where they lie under /root/reference with g++ directly
+(the reference's CMake build system is NOT run).  The handful of headers / one .cpp its configure
+step would generate are hand-written stand-ins under oracle/ref_shim/ (serial, double precision,
+generated kernels ON, no MPI / PETSc / ADIOS2 / Trilinos / MPFR).
+
+Outputs (all under oracle/_ref/, git-ignored, shipped to the GPU box with the snapshot):
+  obj/*.o                 one object per reference translation unit
+  libhyteg_ref.a          walberla::core + libhyteg + constant_stencil_operator (P1 part)
+  ref_dump                oracle/ref_dump.cpp linked against it: dumps golden fixtures (tests/golden/ref_*.npz
+                          are written by oracle/make_ref_fixtures.py from its output) and is the
+                          `bench.py --impl reference` CPU arm
+  libhyteg_ref_kernels.so the stand-alone generated macro-cell kernels (oracle/Makefile, unchanged)
+
+Usage: python oracle/build_ref.py [-j N] [--only-driver]
+"""
+import argparse, os, subprocess, sys, hashlib, concurrent.futures as cf
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+REF = os.environ.get("HYTEG_REF", "/root/reference")
+OUT = os.path.join(HERE, "_ref")
+OBJ = os.path.join(OUT, "obj")
+CXX = os.environ.get("CXX", "g++")
+# x86-64-v3 (AVX2+FMA) instead of -march=native: the library travels to another host (the GPU box).
+FLAGS = ["-O3", "-march=x86-64-v3", "-std=c++20", "-fPIC", "-w", "-DNDEBUG", "-fopenmp-simd",
+         "-I" + os.path.join(HERE, "ref_shim"), "-I" + REF + "/src", "-I" + REF + "/walberla/src",
+         "-I" + REF + "/eigen"]
+
+# sub-trees of the reference that make up the path (walberla::core, libhyteg, the P1 part of
+# constant_stencil_operator).  Directories that need packages this image does not have are left out.
+SKIP_DIRS = ("/petsc/", "/trilinos/", "/python/", "/checkpointrestore/ADIOS2", "/dataexport/ADIOS2",
+             "/egfunctionspace/", "/dgfunctionspace/", "/dg1functionspace/", "/n1e1functionspace/",
+             "/adaptiverefinement/", "/ccrfunctionspace/", "/p0functionspace/", "/experimental/")
+
+
+def sources():
+    src = []
+    for root, _, files in os.walk(REF + "/walberla/src/core"):
+        src += [os.path.join(root, f) for f in files if f.endswith(".cpp") and not f.endswith(".in.cpp")]
+    for root, _, files in os.walk(REF + "/walberla/src/vtk"):
+        src += [os.path.join(root, f) for f in files if f.endswith(".cpp")]
+    for root, _, files in os.walk(REF + "/src/hyteg"):
+        src += [os.path.join(root, f) for f in files if f.endswith(".cpp")]
+    cso = REF + "/src/constant_stencil_operator"
+    src += [os.path.join(cso, f) for f in ("P1ConstantOperator.cpp",)]
+    src += [os.path.join(cso, "P1generatedKernels", f) for f in sorted(os.listdir(cso + "/P1generatedKernels"))
+            if f.endswith(".cpp")]
+    src.append(os.path.join(HERE, "ref_shim", "waLBerlaBuildInfo.cpp"))
+    return [s for s in sorted(src) if not any(d in s for d in SKIP_DIRS)]
+
+
+def obj_name(s):
+    rel = os.path.relpath(s, REF) if s.startswith(REF) else os.path.basename(s)
+    return os.path.join(OBJ, hashlib.md5(rel.encode()).hexdigest()[:8] + "_" + os.path.basename(s)[:-4] + ".o")
+
+
+def compile_one(s):
+    o = obj_name(s)
+    if os.path.exists(o) and os.path.getmtime(o) >= os.path.getmtime(s):
+        return s, 0, ""
+    r = subprocess.run([CXX] + FLAGS + ["-c", s, "-o", o], capture_output=True, text=True)
+    return s, r.returncode, r.stderr[-2000:]
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("-j", type=int, default=os.cpu_count())
+    ap.add_argument("--only-driver", action="store_true")
+    a = ap.parse_args()
+    if not os.path.isdir(REF):
+        print("reference tree not present (%s): keeping prebuilt oracle/_ref" % REF)
+        return 0
+    os.makedirs(OBJ, exist_ok=True)
+    lib = os.path.join(OUT, "libhyteg_ref.a")
+    if not a.only_driver or not os.path.exists(lib):
+        srcs = sources()
+        failed = []
+        with cf.ThreadPoolExecutor(a.j) as ex:
+            for i, (s, rc, err) in enumerate(ex.map(compile_one, srcs)):
+                if rc:
+                    failed.append(s)
+                    print("FAILED", s, "\n", err, file=sys.stderr)
+                elif i % 25 == 0:
+                    print("[%d/%d]" % (i, len(srcs)), flush=True)
+        if failed:
+            print("%d translation units failed (left out of the archive)" % len(failed))
+        objs = [obj_name(s) for s in srcs if s not in failed]
+        if os.path.exists(lib):
+            os.remove(lib)
+        # one `ar` call per chunk: the command line would be too long otherwise
+        for i in range(0, len(objs), 100):
+            subprocess.check_call(["ar", "qc", lib] + objs[i:i + 100])
+        subprocess.check_call(["ranlib", lib])
+    drv = os.path.join(HERE, "ref_dump.cpp")
+    if os.path.exists(drv):
+        subprocess.check_call([CXX] + FLAGS + [drv, os.path.join(HERE, "ref_dump_p2.cpp"), "-o", os.path.join(OUT, "ref_dump"),
+                                               "-Wl,--start-group", lib, "-Wl,--end-group", "-lpthread"])
+        print("built", os.path.join(OUT, "ref_dump"))
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

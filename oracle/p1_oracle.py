@@ -253,30 +253,48 @@ def smooth_jac(o, rhs, src, omega, L, flag, dst=None):
 
 
 def _lex_order(o, L):
-    """HyTeG's sweep order: class by class (vertices, edges, faces, cells), lexicographic inside a
-    macro-cell (x fastest, sor_3D_macrocell_P1.cpp:53-76); inside faces/edges the order induced by the
-    owning (lowest-id) macro-cell's lexicographic order is used."""
+    """HyTeG's sweep order: class by class (vertices, edges, faces, cells), lexicographic inside every primitive in the
+    primitive's OWN index space: a macro-cell in the mesh's vertex order (x fastest, sor_3D_macrocell_P1.cpp:53-76); a
+    macro-face / macro-edge in the order of its vertices SORTED by mesh vertex id (MeshInfo::addFace / addEdge sort them,
+    mesh/MeshInfo.cpp:37-72, and SetupPrimitiveStorage.cpp:126-271 keeps that order), column index fastest
+    (sor_3D_macroface_P1*.cpp, P1Operator.hpp smooth_sor_edge).  Pinned against the reference itself
+    (tests/test_oracle_pinning.py, tests/golden/ref_p1.npz)."""
     lv = o.levels[L]
     if hasattr(lv, "lex"):
         return lv.lex
     seen = np.zeros(lv.n, dtype=bool)
     order = [[] for _ in range(4)]
-    prim_index = {}
     for c in range(len(o.C)):
         for g in lv.cell_map[c]:
             if not seen[g]:
                 seen[g] = True
                 order[lv.dim[g]].append(g)
+    inv_key = {g: key for key, g in lv.key_to_id.items()}
+    # edges: position = weight of the higher vertex; faces: (row = weight of the highest vertex, column = weight of the middle one)
+    order[1].sort(key=lambda g: (lv.prim_of[g], inv_key[g][1][1]))
+    order[2].sort(key=lambda g: (lv.prim_of[g], inv_key[g][2][1], inv_key[g][1][1]))
     lv.lex = order
     return order
 
 
 def smooth_sor(o, x, rhs, omega, L, flag, backwards=False):
-    """P1Operator::smooth_sor (P1Operator.hpp:348-418) in the reference's hybrid ordering."""
+    """P1Operator::smooth_sor (P1Operator.hpp:348-418) in the reference's hybrid ordering: block Gauss-Seidel over the classes
+    vertices -> edges -> faces -> cells (reversed when backwards), block Jacobi between the primitives of a class,
+    lexicographic inside a primitive.
+
+    One more property of the reference is restated, found by pinning against the reference itself: a macro-face reads the
+    points of its neighbour cells through its ghost layers, which are refreshed only by the communicate<Cell,Face> in FRONT of
+    the sweep (P1Operator.hpp:373-379); the communicate<Edge,Face> between the edge and face classes (:403) refreshes the
+    face's own boundary only.  In a forward sweep a face-interior point therefore sees the PRE-SWEEP value of a neighbour that
+    lies on a macro-edge of a neighbour cell which is not an edge of the face itself (stencil direction through the ghost layer).
+    The mirror image in a backward sweep: a macro-edge point sees the PRE-SWEEP value of a neighbour on a macro-face that does
+    not contain the edge (reached through the edge's cell ghost layer, which travels Cell -> Face -> Edge and so carries the
+    cell's copy of that face from before the face class ran)."""
     lv = o.levels[L]
     A = lv.A
     indptr, indices, data = A.indptr, A.indices, A.data
     m = o.mask(L, flag)
+    x0 = x
     x = x.copy()
     order = _lex_order(o, L)
     prim = lv.prim_of
@@ -289,12 +307,17 @@ def smooth_sor(o, x, rhs, omega, L, flag, backwards=False):
                 continue
             s = rhs[g]
             dg = 0.0
+            pg = set(prim[g])
             for k in range(indptr[g], indptr[g + 1]):
                 j = indices[k]
                 if j == g:
                     dg = data[k]
                 elif lv.dim[j] == d and prim[j] != prim[g]:
                     s -= data[k] * snap[j]
+                elif d == 2 and not backwards and lv.dim[j] < 2 and not set(prim[j]) <= pg:
+                    s -= data[k] * x0[j]  # stale ghost layer, see above
+                elif d == 1 and backwards and lv.dim[j] == 2 and not pg <= set(prim[j]):
+                    s -= data[k] * x0[j]  # stale ghost layer, backward sweep
                 else:
                     s -= data[k] * x[j]
             x[g] = (1.0 - omega) * x[g] + omega * s / dg

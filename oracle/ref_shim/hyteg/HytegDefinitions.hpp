@@ -8,3 +8,7 @@ constexpr bool useGeneratedKernels = true;
 }
 } // namespace hyteg
 #define HYTEG_ARCH_ENDIANESS LITTLE_ENDIAN
+// mesh files are always handed to the oracle driver by explicit path; the macro only has to expand to a string
+#ifndef HYTEG_MESH_DIR
+#define HYTEG_MESH_DIR "/root/reference/data/meshes"
+#endif
