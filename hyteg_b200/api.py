@@ -185,8 +185,8 @@ class P1ConstantLaplaceOperator:
     def smooth_jac(self, dst, rhs, src, relax, level, flag):
         self.lib.check(self.lib.dll.hb_operator_smooth_jac(self.h, dst.h, rhs.h, src.h, relax, level, flag))
 
-    def smooth_sor(self, dst, rhs, relax, level, flag, backwards=False):
-        self.lib.check(self.lib.dll.hb_operator_smooth_sor(self.h, dst.h, rhs.h, relax, level, flag, int(backwards)))
+    def smooth_sor(self, dst, rhs, relax, level, flag, backwards=False, ordering=0):
+        self.lib.check(self.lib.dll.hb_operator_smooth_sor_ordered(self.h, dst.h, rhs.h, relax, level, flag, int(backwards), ordering))
 
     def smooth_gs(self, dst, rhs, level, flag):
         self.smooth_sor(dst, rhs, 1.0, level, flag)

@@ -81,6 +81,7 @@ _SIGNATURES = {
     "hb_operator_apply": (C.c_int, [_vp, _vp, _vp, C.c_int, C.c_int, C.c_int]),
     "hb_operator_smooth_jac": (C.c_int, [_vp, _vp, _vp, _vp, C.c_double, C.c_int, C.c_int]),
     "hb_operator_smooth_sor": (C.c_int, [_vp, _vp, _vp, C.c_double, C.c_int, C.c_int, C.c_int]),
+    "hb_operator_smooth_sor_ordered": (C.c_int, [_vp, _vp, _vp, C.c_double, C.c_int, C.c_int, C.c_int, C.c_int]),
     "hb_operator_residual": (C.c_int, [_vp, _vp, _vp, _vp, C.c_int, C.c_int]),
     "hb_operator_cheb_first": (C.c_int, [_vp, _vp, _vp, _vp, C.c_int, C.c_int]),
     "hb_operator_cheb_step": (C.c_int, [_vp, _vp, _vp, _vp, C.c_double, C.c_int, C.c_int]),

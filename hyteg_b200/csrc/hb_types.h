@@ -114,7 +114,10 @@ struct HbIfaceItem
    int32_t  rc0, rc1; // range in regionCopies: the macro-cells containing the point
    uint16_t x, y, z;
    uint8_t  bflag;
-   uint8_t  pad;
+   uint8_t  stage; // 1: a neighbour of the point lies on ANOTHER primitive of the same class and is updated in the same phase, so
+                   // the new value is staged in scratch and committed after a barrier (block Jacobi between primitives of a class,
+                   // P1Operator.hpp:399-411); 0: no other point of the phase reads this one -- it is written in place at once.
+                   // Staged items come first in every phase's list (HbLevelView::ifaceStaged).
 };
 
 struct HbLevelView
@@ -141,6 +144,7 @@ struct HbLevelView
    const HbIfaceItem*  ifaceItems;
    int32_t             ifaceStart[7]; // phase k: [ifaceStart[k], ifaceStart[k+1]); ifaceFaces = 0: phases 3..5 are not listed
    int32_t             ifaceFaces;
+   int32_t             ifaceStaged[6]; // phase k: the items [ifaceStart[k], ifaceStart[k] + ifaceStaged[k]) are staged
    const HbPhaseItem*  phaseItems; // null on levels too large for the single-CTA sweep
    int32_t             phaseStart[HB_NPHASE + 1];
    int32_t             pad1;

@@ -681,6 +681,17 @@ __device__ __forceinline__ void hb_sor_interior_point( const HbLevelView& lv, co
    a.dst[g]       = hb_sor_value( a.omega, c + r, 1.0 / w[D_C], centre, a.rhs[g] );
 }
 
+// writes the new value of an interface point into every local macro-cell array that holds a copy of it
+__device__ __forceinline__ void hb_iface_commit( const HbLevelView& lv, const HbStencilArgs& a, const HbIfaceItem& q, double val )
+{
+   for ( int e = q.rc0; e < q.rc1; e++ )
+   {
+      const HbRegionCopy rc = lv.regionCopies[e];
+      if ( rc.slot < lv.nCells )
+         a.dst[(size_t) rc.slot * lv.cellSize + (size_t) hb_copy_index( lv.N, rc, q.x, q.y, q.z )] = val;
+   }
+}
+
 __global__ void __launch_bounds__( HB_BLOCK, 4 )
     hb_sor_interface_coop_kernel( const HbLevelView lv, HbStencilArgs a, const int backwards, const int kLo, const int kHi, const HbP2PArgs px,
                                   const int interior )
@@ -718,8 +729,10 @@ __global__ void __launch_bounds__( HB_BLOCK, 4 )
       a.bndColour   = k == 0 ? 0 : ( k <= 2 ? k - 1 : k - 3 );
       if ( lv.ifaceItems && ( k <= 2 || lv.ifaceFaces ) )
       {
-         // list form: one load tells a thread its point, the macro-cells containing it and the primitive's boundary flag
-         const int i0 = lv.ifaceStart[k], i1 = lv.ifaceStart[k + 1];
+         // list form: one load tells a thread its point, the macro-cells containing it and the primitive's boundary flag.
+         // Only the points with a same-phase neighbour on another primitive (HbIfaceItem::stage, the first ifaceStaged[k] items
+         // of the list) go through scratch; all others are written to their copies at once.
+         const int i0 = lv.ifaceStart[k], i1 = lv.ifaceStart[k + 1], iS = i0 + lv.ifaceStaged[k];
          const int t0 = i0 + blockIdx.x * blockDim.x + threadIdx.x, stride = gridDim.x * blockDim.x;
          for ( int it = t0; it < i1; it += stride )
          {
@@ -731,20 +744,19 @@ __global__ void __launch_bounds__( HB_BLOCK, 4 )
             const size_t gi = (size_t) q.cell * lv.cellSize + (size_t) hb_index( lv.N, q.x, q.y, q.z );
             double       val;
             hb_epilogue< HB_SOR >( a, &val, gi, sNb, diag, a.srcBase[gi] );
-            a.scratch[it] = val;
+            if ( q.stage )
+               a.scratch[it] = val;
+            else
+               hb_iface_commit( lv, a, q, val );
          }
-         grid.sync();
-         for ( int it = t0; it < i1; it += stride )
+         if ( iS > i0 )
          {
-            const HbIfaceItem q = lv.ifaceItems[it];
-            if ( !( ( a.selMask >> q.bflag ) & 1 ) )
-               continue;
-            const double val = a.scratch[it];
-            for ( int e = q.rc0; e < q.rc1; e++ )
+            grid.sync();
+            for ( int it = t0; it < iS; it += stride )
             {
-               const HbRegionCopy rc = lv.regionCopies[e];
-               if ( rc.slot < lv.nCells )
-                  a.dst[(size_t) rc.slot * lv.cellSize + (size_t) hb_copy_index( lv.N, rc, q.x, q.y, q.z )] = val;
+               const HbIfaceItem q = lv.ifaceItems[it];
+               if ( ( a.selMask >> q.bflag ) & 1 )
+                  hb_iface_commit( lv, a, q, a.scratch[it] );
             }
          }
       }

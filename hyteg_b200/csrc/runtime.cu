@@ -131,8 +131,24 @@ void hb_storage::buildPhaseItems( hb::LevelTables& lt )
    {
       // cooperative interface launch: per-phase lists of the points this rank evaluates (rank-local owners)
       static_assert( sizeof( HbIfaceItem ) == 20, "HbIfaceItem layout" );
-      v.ifaceFaces = v.N <= 128 ? 1 : 0;
+      v.ifaceFaces = v.N <= hb::tuning( "sor_iface_lists_max_n", 1024 ) ? 1 : 0;
       std::vector< std::vector< HbIfaceItem > > lists( 6 );
+      const int N = v.N;
+      static const int dirs[14][3] = { { -1, 0, 0 }, { 1, 0, 0 }, { 0, 1, 0 }, { 0, -1, 0 }, { -1, 1, 0 }, { 1, -1, 0 }, { 0, 0, 1 },
+                                       { -1, 0, 1 }, { 0, -1, 1 }, { 1, -1, 1 }, { 0, 0, -1 }, { 0, 1, -1 }, { 1, 0, -1 }, { -1, 1, -1 } };
+      // the macro primitive a point lies on, as the sorted global ids of its macro vertices packed into one key
+      auto primKey = [N]( const HbCellInfo& ci, int x, int y, int z ) {
+         const int b[4] = { N - x - y - z, x, y, z };
+         int       g[4], n = 0;
+         for ( int j = 0; j < 4; j++ )
+            if ( b[j] != 0 )
+               g[n++] = ci.gv[j];
+         std::sort( g, g + n );
+         unsigned long long key = (unsigned long long) n;
+         for ( int j = 0; j < n; j++ )
+            key = key * 2097152ull + (unsigned long long) ( g[j] + 1 );
+         return key;
+      };
       for ( int c = 0; c < view.nLocal; c++ )
       {
          const HbCellInfo& ci = view.cells[c];
@@ -151,8 +167,40 @@ void hb_storage::buildPhaseItems( hb::LevelTables& lt )
             q.y     = p.y;
             q.z     = p.z;
             q.bflag = (uint8_t) reg.bflag;
+            // staged?  look at every neighbour of the point in every macro-cell that contains it
+            const unsigned long long own = primKey( ci, p.x, p.y, p.z );
+            for ( int e = q.rc0; e < q.rc1 && !q.stage; e++ )
+            {
+               const HbRegionCopy& rc = view.regionCopies[e];
+               const HbCellInfo&   cj = view.cells[rc.slot];
+               int                 P[3];
+               for ( int r = 0; r < 3; r++ )
+                  P[r] = rc.c[r][0] * N + rc.c[r][1] * p.x + rc.c[r][2] * p.y + rc.c[r][3] * p.z;
+               for ( int d = 0; d < 14 && !q.stage; d++ )
+               {
+                  const int X = P[0] + dirs[d][0], Y = P[1] + dirs[d][1], Z = P[2] + dirs[d][2];
+                  if ( X < 0 || Y < 0 || Z < 0 || X + Y + Z > N )
+                     continue;
+                  const int mq = hb_mask( N, X, Y, Z );
+                  if ( mq == 0 || cj.region[mq].dim != reg.dim )
+                     continue;
+                  if ( hb_interface_colour( cj, N, X, Y, Z ) == colour && primKey( cj, X, Y, Z ) != own )
+                     q.stage = 1;
+               }
+            }
             lists[k].push_back( q );
          }
+      }
+      for ( int k = 0; k < 6; k++ )
+      {
+         std::stable_sort( lists[k].begin(), lists[k].end(), []( const HbIfaceItem& a, const HbIfaceItem& b ) { return a.stage > b.stage; } );
+         int n = 0;
+         while ( n < (int) lists[k].size() && lists[k][n].stage )
+            n++;
+         v.ifaceStaged[k] = hb::tuning( "sor_stage_all", 0 ) ? (int) lists[k].size() : n;
+         if ( hb::tuning( "sor_stage_all", 0 ) )
+            for ( auto& it : lists[k] )
+               it.stage = 1;
       }
       std::vector< HbIfaceItem > all;
       for ( int k = 0; k < 6; k++ )
@@ -263,6 +311,8 @@ hb::LevelTables& hb_storage::level( int L )
       lt->items.upload( items );
       hb_shuffle_build_items( N, items, hb::tuning( "shuffle_ys", 0 ), hb::tuning( "shuffle_order", 0 ) );
       lt->itemsShuffle.upload( items );
+      hb_shuffle_build_items( N, items, N, 0 ); // a line along y must not be split between CTAs (sequential along the line)
+      lt->itemsLine.upload( items );
    }
    lt->scratch.alloc( (size_t) view.nLocal * bnd.size() );
    HbLevelView& v = lt->view;

@@ -27,6 +27,7 @@ struct HbStreamArgs
    int32_t       sync;      // shuffle kernel: pace the warps of a CTA with a named barrier per unrolled block
    int32_t       cellMajor; // shuffle kernel: block id = cell * nItems + item (else item * nCells + cell)
    int32_t*      counter; // [2] work counter + finished-CTA counter, both zero between launches
+   int32_t       cellFirst, cellCount; // shuffle kernel: the launch covers macro-cells [cellFirst, cellFirst + cellCount) (cellCount 0: all)
 };
 
 // true if 'mode' on this level runs through the streamed kernel (N >= 32 and a streamed mode)

@@ -55,6 +55,12 @@ class P1ConstantLaplaceOperator
    {
       hbCheck( hb_operator_smooth_sor( op_, dst.handle(), rhs.handle(), relax, (int) level, (int) flag, 1 ) );
    }
+   /// not in the reference: the sweep with the interior ordering named (0 default, 1 four colours everywhere -- forward and backward
+   /// sweeps of ordering 1 are exact transposes of each other; hyteg_b200.h hb_operator_smooth_sor_ordered)
+   void smooth_sor_ordered( const srcType& dst, const srcType& rhs, real_t relax, size_t level, DoFType flag, bool backwards, int ordering ) const
+   {
+      hbCheck( hb_operator_smooth_sor_ordered( op_, dst.handle(), rhs.handle(), relax, (int) level, (int) flag, backwards ? 1 : 0, ordering ) );
+   }
    void smooth_jac( const srcType& dst, const srcType& rhs, const srcType& src, real_t relax, size_t level, DoFType flag ) const
    {
       hbCheck( hb_operator_smooth_jac( op_, dst.handle(), rhs.handle(), src.handle(), relax, (int) level, (int) flag ) );
@@ -189,8 +195,9 @@ class SymmetricGaussSeidelSmoother : public Solver< OperatorType >
  public:
    void solve( const OperatorType& A, const typename OperatorType::srcType& x, const typename OperatorType::srcType& b, const uint_t level ) override
    {
-      A.smooth_gs( x, b, level, Inner | NeumannBoundary | FreeslipBoundary );
-      A.smooth_gs_backwards( x, b, level, Inner | NeumannBoundary | FreeslipBoundary );
+      // the pair must be a forward sweep and its exact transpose (the smoother is used as a symmetric preconditioner as well)
+      A.smooth_sor_ordered( x, b, 1.0, level, Inner | NeumannBoundary | FreeslipBoundary, false, 1 );
+      A.smooth_sor_ordered( x, b, 1.0, level, Inner | NeumannBoundary | FreeslipBoundary, true, 1 );
    }
 };
 

@@ -324,27 +324,89 @@ def smooth_sor(o, x, rhs, omega, L, flag, backwards=False):
     return x
 
 
+def _multicolour_phases(o, L, interior):
+    """Phases of the DEVICE ordering (hyteg_b200/csrc/runtime_operator.inc hb_operator_smooth_sor_ordered), each a list of
+    index arrays that are updated simultaneously, in forward order:
+      0      macro vertices
+      1, 2   macro-edge points by parity of the barycentric weight of the edge's higher vertex
+      3..5   macro-face points by (w_mid + 2 w_high) mod 3 (weights w.r.t. the face's vertices sorted by global id)
+      then the macro-cell interiors: interior == "c4": four colours (x + 2y + 3z) mod 4;
+      interior == "line": lines along y in three colours (x + 2z) mod 3, Gauss-Seidel along each line in ascending y
+      (one simultaneous update per (colour, y))."""
+    lv = o.levels[L]
+    key = ("mc", interior)
+    if hasattr(lv, "mc") and key in lv.mc:
+        return lv.mc[key]
+    inv_key = {g: k for k, g in lv.key_to_id.items()}
+    ph = [[] for _ in range(6)]
+    for g in range(lv.n):
+        k = inv_key[g]
+        if len(k) == 1:
+            ph[0].append(g)
+        elif len(k) == 2:
+            ph[1 + (k[1][1] & 1)].append(g)
+        elif len(k) == 3:
+            ph[3 + (k[1][1] + 2 * k[2][1]) % 3].append(g)
+    phases = [np.array(p, dtype=np.int64) for p in ph]
+    pts, N = lv.pts, lv.N
+    inter = (pts[:, 0] > 0) & (pts[:, 1] > 0) & (pts[:, 2] > 0) & (pts.sum(1) < N)
+    idx = np.nonzero(inter)[0]
+    x_, y_, z_ = pts[idx, 0], pts[idx, 1], pts[idx, 2]
+    if interior == "c4":
+        col = (x_ + 2 * y_ + 3 * z_) % 4
+        for c in range(4):
+            phases.append(np.concatenate([lv.cell_map[k][idx[col == c]] for k in range(len(o.C))]) if len(idx) else np.zeros(0, dtype=np.int64))
+    else:
+        col = (x_ + 2 * z_) % 3
+        for c in range(3):
+            for y in range(1, N - 1):
+                sel = idx[(col == c) & (y_ == y)]
+                if len(sel):
+                    phases.append(np.concatenate([lv.cell_map[k][sel] for k in range(len(o.C))]))
+    if not hasattr(lv, "mc"):
+        lv.mc = {}
+    lv.mc[key] = phases
+    return phases
+
+
+def smooth_sor_multicolour(o, x, rhs, omega, L, flag, backwards=False, interior="c4"):
+    """The device's multicolour restatement of P1Operator::smooth_sor: same class order as the reference (vertices, edges,
+    faces, cells; reversed when backwards) and block Jacobi between the primitives of a class, but colours instead of the
+    lexicographic order inside a primitive.  Every phase is a simultaneous update."""
+    lv = o.levels[L]
+    m = o.mask(L, flag)
+    x = x.copy()
+    phases = _multicolour_phases(o, L, interior)
+    for g in (phases[::-1] if backwards else phases):
+        g = g[m[g]]
+        if len(g) == 0:
+            continue
+        r = rhs[g] - lv.A[g] @ x
+        x[g] = x[g] + omega * r / lv.diag[g]
+    return x
+
+
 def cheb_coefficients(order, lower, upper):
-    """ChebyshevSmoother::setupCoefficientsInternal (ChebyshevSmoother.hpp:328-400), orders 1..4"""
+    """ChebyshevSmoother::setupCoefficientsInternal (ChebyshevSmoother.hpp:329-539).  The reference tabulates closed forms for
+    orders 1..10; they are the monomial coefficients c_i of the polynomial p with
+        1 - lambda p(lambda) = T_k( (theta - lambda) / delta ) / T_k( theta / delta ),   p = sum_i c_i lambda^i,
+    (the smoother applies x += sum_i c_i (D^-1 A)^i D^-1 r, ChebyshevSmoother.hpp:179-222).  Restated here from that
+    definition with exact polynomial algebra; pinned against the reference's own tables for orders 1..10
+    (tests/golden/ref_p1.npz: cheb_coeffs_order*)."""
+    from numpy.polynomial import chebyshev as C, polynomial as P
     theta = 0.5 * (upper + lower)
     delta = 0.5 * (upper - lower)
-    if order == 1:
-        return [1.0 / theta]
-    if order == 2:
-        t0 = 1.0 / (delta ** 2 - 2 * theta ** 2)
-        return [-4 * theta * t0, 2 * t0]
-    if order == 3:
-        t0 = 3 * delta ** 2
-        t1 = theta ** 2
-        t2 = 1.0 / (-4 * theta ** 3 + theta * t0)
-        return [t2 * (t0 - 12 * t1), 12 / (t0 - 4 * t1), -4 * t2]
-    if order == 4:
-        t0 = delta ** 2
-        t1 = theta ** 2
-        t2 = 8 * t0
-        t3 = 1.0 / (delta ** 4 + 8 * theta ** 4 - t1 * t2)
-        return [t3 * (32 * theta ** 3 - 16 * theta * t0), t3 * (-48 * t1 + t2), 32 * theta * t3, -8 * t3]
-    raise ValueError("oracle restates orders 1..4")
+    tk = C.cheb2poly([0.0] * order + [1.0])  # T_k(s) in powers of s
+    # substitute s = (theta - lambda) / delta
+    lin = np.array([theta / delta, -1.0 / delta])
+    q = np.zeros(1)
+    pw = np.ones(1)
+    for a in tk:
+        q = P.polyadd(q, a * pw)
+        pw = P.polymul(pw, lin)
+    q = q / P.polyval(0.0, q)  # T_k((theta - lambda)/delta) / T_k(theta/delta): value 1 at lambda = 0
+    one_minus = P.polysub(np.ones(1), q)  # = lambda p(lambda): constant term vanishes
+    return [float(c) for c in one_minus[1:order + 1]]
 
 
 def chebyshev(o, x, b, coeffs, L, flag=SMOOTH_FLAG):

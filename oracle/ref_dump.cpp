@@ -155,6 +155,13 @@ void dumpP1( const P1Function< real_t >& f, uint_t level, const std::string& pat
 using namespace refdump;
 using Op = P1ConstantLaplaceOperator;
 
+// ChebyshevSmoother keeps its coefficients protected: a derived class reads them out
+struct ChebPeek : ChebyshevSmoother< Op >
+{
+   using ChebyshevSmoother< Op >::ChebyshevSmoother;
+   const std::vector< real_t >& coeffs( uint_t i ) const { return coefficients[i]; }
+};
+
 static double now()
 {
    return std::chrono::duration< double >( std::chrono::steady_clock::now().time_since_epoch() ).count();
@@ -212,6 +219,7 @@ int main( int argc, char** argv )
    else if ( a.cmd == "sor" || a.cmd == "jac" || a.cmd == "cheb" || a.cmd == "sgs" )
    {
       Op                   A( st, L, L );
+      A.computeInverseDiagonalOperatorValues();
       P1Function< real_t > x( "x", st, L, L ), b( "b", st, L, L ), tmp( "tmp", st, L, L ), ev( "ev", st, L, L );
       setFromCloud( x, a.str( "x" ), h, L );
       setFromCloud( b, a.str( "rhs" ), h, L );
@@ -264,6 +272,7 @@ int main( int argc, char** argv )
    else if ( a.cmd == "gmg" )
    {
       Op                   A( st, minL, L );
+      A.computeInverseDiagonalOperatorValues();
       P1Function< real_t > x( "x", st, minL, L ), b( "b", st, minL, L ), r( "r", st, minL, L ), one( "one", st, minL, L ),
           ev( "ev", st, minL, L ), tmp( "tmp", st, minL, L );
       setFromCloud( x, a.str( "x" ), h, L );
@@ -302,9 +311,21 @@ int main( int argc, char** argv )
       }
       dumpP1( x, L, a.str( "out" ) );
    }
+   else if ( a.cmd == "chebcoeffs" )
+   {
+      // ChebyshevSmoother::setupCoefficients( order, lower, upper ) for orders 1..10 (ChebyshevSmoother.hpp:278-539)
+      for ( uint_t order = 1; order <= 10; order++ )
+      {
+         ChebPeek cheb( st, L, L );
+         cheb.setupCoefficientsInternal( order, a.num( "lower", 0.3 ), a.num( "upper", 1.2 ), L );
+         for ( real_t c : cheb.coeffs( 0 ) )
+            std::printf( "RESULT order%d %.17g\n", int( order ), c );
+      }
+   }
    else if ( a.cmd == "radius" )
    {
       Op                   A( st, L, L );
+      A.computeInverseDiagonalOperatorValues();
       P1Function< real_t > x( "x", st, L, L ), tmp( "tmp", st, L, L );
       setFromCloud( x, a.str( "x" ), h, L );
       std::printf( "RESULT rho %.17g\n", chebyshev::estimateRadius( A, L, uint_t( a.num( "iterations", 20 ) ), st, x, tmp ) );
@@ -330,6 +351,7 @@ int main( int argc, char** argv )
    {
       // the reference's stock timed call (apps/benchmarks/ApplyBenchmark/ApplyBenchmark.cpp:87): A.apply( src, dst, level, Inner )
       Op                   A( st, minL, L );
+      A.computeInverseDiagonalOperatorValues();
       P1Function< real_t > src( "src", st, minL, L ), dst( "dst", st, minL, L ), b( "b", st, minL, L );
       std::function< real_t( const Point3D& ) > fn = []( const Point3D& p ) { return std::sin( p[0] ) * std::sinh( p[1] ) + p[2]; };
       src.interpolate( fn, L, All );

@@ -39,7 +39,7 @@ def make_cell_sweep(o, L, scheme, omega=1.0):
         colours = ((2 * y_ + z_) % 3) * 2 + (x_ % 2)
     elif scheme == "c8":
         colours = (x_ % 2) + 2 * (y_ % 2) + 4 * (z_ % 2)
-    elif scheme.startswith("ylex3") or scheme in ("c3liney", "c3rowx"):
+    elif scheme.startswith("ylex3") or scheme.startswith("tile3") or scheme in ("c3liney", "c3rowx"):
         # sequential in y, 3 colours (x+2z)%3 inside a y-plane; tiles in (x,z) are block-Jacobi (tile TXxTZ)
         colours = None
     # global ids per cell
@@ -64,6 +64,13 @@ def make_cell_sweep(o, L, scheme, omega=1.0):
         block = np.zeros(len(idx), dtype=np.int64)
     elif scheme == "c3liney":
         order = np.lexsort((y_, x_, z_, (x_ + 2 * z_) % 3))
+        block = np.zeros(len(idx), dtype=np.int64)
+    elif scheme.startswith("tile3"):
+        # tiles in (x,z) coloured (i + 2j) % 3; inside a tile: lines along y coloured (x+2z)%3, sequential along y
+        _, TX, TZ = scheme.split("_")
+        TX, TZ = int(TX), int(TZ)
+        ti, tj = (x_ - 1) // TX, (z_ - 1) // TZ
+        order = np.lexsort((y_, x_, z_, (x_ + 2 * z_) % 3, tj, ti, (ti + 2 * tj) % 3))
         block = np.zeros(len(idx), dtype=np.int64)
     elif scheme == "c3rowx":
         order = np.lexsort((x_, y_, z_, (y_ + 2 * z_) % 3))
