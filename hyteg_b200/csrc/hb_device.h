@@ -79,8 +79,7 @@ enum HbMode
    HB_CHEB_FIRST,        // dst  = D^-1 (rhs - A src)
    HB_CHEB_STEP,         // dst  = D^-1 A src ; aux += omega * src
    HB_DIAG,              // dst  = diag(A)
-   HB_INVDIAG,           // dst  = 1/diag(A)
-   HB_SOR_LINE           // shuffle kernel only: SOR in place, lines along y in three colours (x + 2z) mod 3, sequential along the line
+   HB_INVDIAG            // dst  = 1/diag(A)
 };
 
 struct HbStencilArgs

@@ -311,8 +311,6 @@ hb::LevelTables& hb_storage::level( int L )
       lt->items.upload( items );
       hb_shuffle_build_items( N, items, hb::tuning( "shuffle_ys", 0 ), hb::tuning( "shuffle_order", 0 ) );
       lt->itemsShuffle.upload( items );
-      hb_shuffle_build_items( N, items, N, 0 ); // a line along y must not be split between CTAs (sequential along the line)
-      lt->itemsLine.upload( items );
    }
    lt->scratch.alloc( (size_t) view.nLocal * bnd.size() );
    HbLevelView& v = lt->view;

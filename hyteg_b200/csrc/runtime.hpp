@@ -71,7 +71,6 @@ struct LevelTables
    DeviceBuffer< HbChunkDesc > descs; // per (local macro-cell, chunk), rebuilt with the topology tables
    DeviceBuffer< HbItem >     items;   // work items of the TMA-streamed interior kernel
    DeviceBuffer< HbItem >     itemsShuffle; // work items of the centre-column + shuffle interior kernel
-   DeviceBuffer< HbItem >     itemsLine;    // the same kernel's items for the line-coloured SOR: every item spans ALL rows of its columns
    DeviceBuffer< double >     scratch; // nCells*nBnd, interface staging (SOR)
    std::vector< HbBndPoint >  hXyz;    // host copy of the coordinate template
 

@@ -75,7 +75,7 @@ __device__ __forceinline__ double epilogue( const HbStencilArgs& a, double Ax, d
       return centre + a.omega * ( invd * ( e - Ax ) );
    if ( MODE == HB_CHEB_FIRST )
       return invd * ( e - Ax );
-   if ( MODE == HB_SOR || MODE == HB_SOR_LINE ) // e = rhs; Ax includes the centre term: invd * ( rhs - sum over neighbours ) = invd * ( e - Ax ) + centre
+   if ( MODE == HB_SOR ) // e = rhs; Ax includes the centre term: invd * ( rhs - sum over neighbours ) = invd * ( e - Ax ) + centre
       return hb_sor_value( a.omega, Ax, invd, centre, e );
    if ( MODE == HB_CHEB_STEP ) // second store ( aux = e + omega * centre ) is issued by the caller
       return invd * Ax;
@@ -157,22 +157,16 @@ __global__ void __maxnreg__( REGS ) hb_shuffle_kernel( const HbLevelView lv, con
    int        r0 = ( sa.sync & 4 ) ? 0 : max( 0, yMax0 - ya + 1 ), r1 = ( sa.sync & 4 ) ? 0 : max( 0, yMax1 - ya + 1 ); // rows this lane still has to store in slice zA / zA+1
    // SOR: colour (x + 2y + 3z) mod 4 of the output point (same colouring as the generic kernel); k0 == 0 mod 4 <=> slice zA matches
    int k0 = ( MODE == HB_SOR ) ? ( xc + 2 * ya + 3 * zA - a.colour ) : 0;
-   // SOR_LINE: the lines along y (fixed x, z) are coloured (x + 2z) mod 3 -- lines of one colour are not coupled, so a pass
-   // over one colour is free of races in place -- and a lane walks its line in ascending y with the value it has just
-   // written as the S neighbour of the next row (true Gauss-Seidel along the line).  own0 / own1: the lane's column is a
-   // line of this pass's colour in slice zA / zA+1 (never both).
-   const bool own0 = ( MODE == HB_SOR_LINE ) && ( ( xc + 2 * zA + 3 - a.colour ) % 3 == 0 );
-   const bool own1 = ( MODE == HB_SOR_LINE ) && ( ( xc + 2 * zA + 5 - a.colour ) % 3 == 0 );
 
    auto rowAddr = [&]( u64 P, int pitch, int j, int q ) -> u64 { return P + (u64) ( (long long) pitch * ( 8 * j ) + (long long) ( -8 * ( j * ( j - 1 ) / 2 + q * j ) ) ); };
    auto load    = [&]( double& v, u64 addr, bool pred ) {
-      if ( MODE == HB_SOR || MODE == HB_SOR_LINE ) // SOR updates the array it reads (only points of other colours matter): coherent loads
+      if ( MODE == HB_SOR ) // SOR updates the array it reads (only points of other colours matter): coherent loads
          asm volatile( "{\n .reg .pred p;\n setp.ne.s32 p, %2, 0;\n @p ld.global.f64 %0, [%1];\n}" : "+d"( v ) : "l"( addr ), "r"( (int) pred ) : "memory" );
       else
          asm( "{\n .reg .pred p;\n setp.ne.s32 p, %2, 0;\n @p ld.global.nc.f64 %0, [%1];\n}" : "+d"( v ) : "l"( addr ), "r"( (int) pred ) );
    };
    auto loadNow = [&]( double& v, u64 addr ) {
-      if ( MODE == HB_SOR || MODE == HB_SOR_LINE )
+      if ( MODE == HB_SOR )
          asm volatile( "ld.global.f64 %0, [%1];" : "=d"( v ) : "l"( addr ) : "memory" );
       else
          asm( "ld.global.nc.f64 %0, [%1];" : "=d"( v ) : "l"( addr ) );
@@ -268,12 +262,10 @@ __global__ void __maxnreg__( REGS ) hb_shuffle_kernel( const HbLevelView lv, con
          l1        = fma( w[D_BNW], N1, l1 );
          l1        = fma( w[D_TW], B3, l1 );
          // centre-column taps, seeded with the left neighbour's partial sum.  output (zA, y): below = slice 0, own = 1, above = 2
-         // (SOR_LINE: the S tap -- the value written one row earlier -- enters last: one fma on the loop-carried chain)
          double c0 = __shfl_up_sync( 0xffffffffu, l0, 1 );
          c0        = fma( w[D_C], B1, c0 );
          c0        = fma( w[D_N], N1, c0 );
-         if ( MODE != HB_SOR_LINE )
-            c0 = fma( w[D_S], A1, c0 );
+         c0        = fma( w[D_S], A1, c0 );
          c0        = fma( w[D_BC], B0, c0 );
          c0        = fma( w[D_BN], N0, c0 );
          c0        = fma( w[D_TC], B2, c0 );
@@ -282,8 +274,7 @@ __global__ void __maxnreg__( REGS ) hb_shuffle_kernel( const HbLevelView lv, con
          double c1 = __shfl_up_sync( 0xffffffffu, l1, 1 );
          c1        = fma( w[D_C], B2, c1 );
          c1        = fma( w[D_N], N2, c1 );
-         if ( MODE != HB_SOR_LINE )
-            c1 = fma( w[D_S], A2, c1 );
+         c1        = fma( w[D_S], A2, c1 );
          c1        = fma( w[D_BC], B1, c1 );
          c1        = fma( w[D_BN], N1, c1 );
          c1        = fma( w[D_TC], B3, c1 );
@@ -315,11 +306,6 @@ __global__ void __maxnreg__( REGS ) hb_shuffle_kernel( const HbLevelView lv, con
             r1v        = fma( w[D_TSE], A3, r1v );
             Ax0        = c0 + __shfl_down_sync( 0xffffffffu, r0v, 1 );
             Ax1        = c1 + __shfl_down_sync( 0xffffffffu, r1v, 1 );
-            if ( MODE == HB_SOR_LINE )
-            {
-               Ax0 = fma( w[D_S], A1, Ax0 );
-               Ax1 = fma( w[D_S], A2, Ax1 );
-            }
          }
 
          bool s0 = u < r0, s1 = u < r1;
@@ -328,26 +314,20 @@ __global__ void __maxnreg__( REGS ) hb_shuffle_kernel( const HbLevelView lv, con
             s0 = s0 && ( km == ( ( 4 - 2 * u ) & 3 ) );
             s1 = s1 && ( km == ( ( 1 - 2 * u ) & 3 ) ); // k0 + 3 + 2u == 0 mod 4
          }
-         if ( MODE == HB_SOR_LINE )
-         {
-            s0 = s0 && own0;
-            s1 = s1 && own1;
-         }
          const u64 q0 = rowAddr( O0, so, u, 0 ), q1 = rowAddr( O1, so, u, 1 );
-         const double v0 = epilogue< MODE >( a, Ax0, invd, B1, x0 ), v1 = epilogue< MODE >( a, Ax1, invd, B2, x1 );
-         store( q0, v0, s0 );
-         store( q1, v1, s1 );
+         store( q0, epilogue< MODE >( a, Ax0, invd, B1, x0 ), s0 );
+         store( q1, epilogue< MODE >( a, Ax1, invd, B2, x1 ), s1 );
          if ( MODE == HB_CHEB_STEP )
          {
             store( q0 + (u64) auxOff, x0 + a.omega * B1, s0 );
             store( q1 + (u64) auxOff, x1 + a.omega * B2, s1 );
          }
 
-         // slide the window (SOR_LINE: the row just written is the S row of the next one)
+         // slide the window
          B0 = N0;
-         A1 = ( MODE == HB_SOR_LINE && s0 ) ? v0 : B1;
+         A1 = B1;
          B1 = N1;
-         A2 = ( MODE == HB_SOR_LINE && s1 ) ? v1 : B2;
+         A2 = B2;
          B2 = N2;
          A3 = B3;
          B3 = N3;
@@ -413,7 +393,7 @@ bool hb_shuffle_supported( int mode, const HbLevelView& lv )
    if ( lv.N < 32 || lv.nCells == 0 || lv.nCells > HB_CONST_W_ENTRIES )
       return false;
    return mode == HB_APPLY_REPLACE || mode == HB_APPLY_ADD || mode == HB_RESIDUAL || mode == HB_JACOBI || mode == HB_CHEB_FIRST ||
-          mode == HB_CHEB_STEP || mode == HB_SOR || mode == HB_SOR_LINE;
+          mode == HB_CHEB_STEP || mode == HB_SOR;
 }
 
 // experimental register budgets (more resident CTAs per SM): apply and Jacobi only
@@ -458,9 +438,6 @@ static void launchDepth( int mode, unsigned g, unsigned b, const HbLevelView& lv
       break;
    case HB_SOR:
       hb_shuffle_kernel< HB_SOR, DEPTH ><<< g, b, 0, st >>>( lv, a, sa );
-      break;
-   case HB_SOR_LINE:
-      hb_shuffle_kernel< HB_SOR_LINE, DEPTH ><<< g, b, 0, st >>>( lv, a, sa );
       break;
    default:
       throw std::runtime_error( "hyteg_b200: mode not supported by the shuffle kernel" );

@@ -155,9 +155,8 @@ int hb_operator_apply( hb_operator* op, const hb_function* src, hb_function* dst
 int hb_operator_smooth_jac( hb_operator* op, hb_function* dst, const hb_function* rhs, const hb_function* src, double omega, int level, int flag );
 /* P1Operator::smooth_sor / smooth_sor_backwards / smooth_gs (P1Operator.hpp:322-427): multicolour ordering */
 int hb_operator_smooth_sor( hb_operator* op, hb_function* dst, const hb_function* rhs, double omega, int level, int flag, int backwards );
-/* same with the interior ordering chosen by the caller: 0 = default (forward sweeps on levels >= 7 walk the lines along y in three
- * colours, Gauss-Seidel along each line; everything else four colours), 1 = four colours everywhere -- a forward and a backward sweep
- * with ordering 1 are exact transposes of each other (SymmetricGaussSeidelSmoother.hpp pairs them) */
+/* same with the interior ordering named by the caller.  Both 0 and 1 currently select the four-colour ordering (x + 2y + 3z) mod 4 on
+ * every level; a forward and a backward sweep of it are exact transposes of each other (SymmetricGaussSeidelSmoother.hpp pairs them). */
 int hb_operator_smooth_sor_ordered( hb_operator* op, hb_function* dst, const hb_function* rhs, double omega, int level, int flag, int backwards, int ordering );
 /* fused r = b - A x  (GeometricMultigridSolver.hpp:255-259 does apply + assign) */
 int hb_operator_residual( hb_operator* op, const hb_function* x, const hb_function* b, hb_function* r, int level, int flag );

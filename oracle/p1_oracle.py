@@ -330,9 +330,7 @@ def _multicolour_phases(o, L, interior):
       0      macro vertices
       1, 2   macro-edge points by parity of the barycentric weight of the edge's higher vertex
       3..5   macro-face points by (w_mid + 2 w_high) mod 3 (weights w.r.t. the face's vertices sorted by global id)
-      then the macro-cell interiors: interior == "c4": four colours (x + 2y + 3z) mod 4;
-      interior == "line": lines along y in three colours (x + 2z) mod 3, Gauss-Seidel along each line in ascending y
-      (one simultaneous update per (colour, y))."""
+      then the macro-cell interiors in four colours (x + 2y + 3z) mod 4 (a proper colouring of the 15-point stencil graph)."""
     lv = o.levels[L]
     key = ("mc", interior)
     if hasattr(lv, "mc") and key in lv.mc:
@@ -352,17 +350,10 @@ def _multicolour_phases(o, L, interior):
     inter = (pts[:, 0] > 0) & (pts[:, 1] > 0) & (pts[:, 2] > 0) & (pts.sum(1) < N)
     idx = np.nonzero(inter)[0]
     x_, y_, z_ = pts[idx, 0], pts[idx, 1], pts[idx, 2]
-    if interior == "c4":
-        col = (x_ + 2 * y_ + 3 * z_) % 4
-        for c in range(4):
-            phases.append(np.concatenate([lv.cell_map[k][idx[col == c]] for k in range(len(o.C))]) if len(idx) else np.zeros(0, dtype=np.int64))
-    else:
-        col = (x_ + 2 * z_) % 3
-        for c in range(3):
-            for y in range(1, N - 1):
-                sel = idx[(col == c) & (y_ == y)]
-                if len(sel):
-                    phases.append(np.concatenate([lv.cell_map[k][sel] for k in range(len(o.C))]))
+    assert interior == "c4"
+    col = (x_ + 2 * y_ + 3 * z_) % 4
+    for c in range(4):
+        phases.append(np.concatenate([lv.cell_map[k][idx[col == c]] for k in range(len(o.C))]) if len(idx) else np.zeros(0, dtype=np.int64))
     if not hasattr(lv, "mc"):
         lv.mc = {}
     lv.mc[key] = phases

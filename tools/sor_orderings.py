@@ -39,7 +39,7 @@ def make_cell_sweep(o, L, scheme, omega=1.0):
         colours = ((2 * y_ + z_) % 3) * 2 + (x_ % 2)
     elif scheme == "c8":
         colours = (x_ % 2) + 2 * (y_ % 2) + 4 * (z_ % 2)
-    elif scheme.startswith("ylex3") or scheme.startswith("tile3") or scheme in ("c3liney", "c3rowx"):
+    elif scheme.startswith("ylex3") or scheme.startswith("tile3") or scheme.startswith("tile4") or scheme in ("c3liney", "c3rowx"):
         # sequential in y, 3 colours (x+2z)%3 inside a y-plane; tiles in (x,z) are block-Jacobi (tile TXxTZ)
         colours = None
     # global ids per cell
@@ -71,6 +71,13 @@ def make_cell_sweep(o, L, scheme, omega=1.0):
         TX, TZ = int(TX), int(TZ)
         ti, tj = (x_ - 1) // TX, (z_ - 1) // TZ
         order = np.lexsort((y_, x_, z_, (x_ + 2 * z_) % 3, tj, ti, (ti + 2 * tj) % 3))
+        block = np.zeros(len(idx), dtype=np.int64)
+    elif scheme.startswith("tile4"):
+        # tiles in (x,y,z) coloured (i + 2k + 3j) % 4; inside a tile: lines along y coloured (x+2z)%3, sequential along y
+        _, TX, TY, TZ = scheme.split("_")
+        TX, TY, TZ = int(TX), int(TY), int(TZ)
+        ti, tk, tj = (x_ - 1) // TX, (y_ - 1) // TY, (z_ - 1) // TZ
+        order = np.lexsort((y_, x_, z_, (x_ + 2 * z_) % 3, tk, tj, ti, (ti + 2 * tk + 3 * tj) % 4))
         block = np.zeros(len(idx), dtype=np.int64)
     elif scheme == "c3rowx":
         order = np.lexsort((x_, y_, z_, (y_ + 2 * z_) % 3))
