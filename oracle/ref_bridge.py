@@ -84,3 +84,20 @@ def to_global(xyz_global, cloud, tol):
     assert not np.isnan(out).any()
     assert np.array_equal(out[idx], val), "copies of a DoF disagree in the reference dump"
     return out
+
+
+def p2_apply(session, o, x, level, form="divkgrad", dst=None, flag=1, update=0, shell=0, **kw):
+    """P2ElementwiseOperator< form >::apply of the reference on the P2 vector x (oracle numbering: vertex DoFs, then edge DoFs);
+    inputs travel as ONE cloud in PHYSICAL coordinates (P2Function::interpolate evaluates at the blended position), the result comes
+    back as a vertex cloud and an edge cloud in COMPUTATIONAL coordinates"""
+    phys = o.dof_physical_coordinates()
+    args = dict(src=session.cloud(phys, x), form=form, flag=flag, update=update, shell=shell, **kw)
+    if dst is not None:
+        args["dst"] = session.cloud(phys, dst)
+    oute = os.path.join(session.dir, "oute%d.bin" % session.n)
+    res, cl = session.run("p2apply", level, oute=oute, **args)
+    de = np.fromfile(oute, dtype=np.float64).reshape(-1, 4)
+    tol = 0.05 * min_spacing(session.v, session.c, level)
+    v = to_global(o.xyz[: o.nv], cl, tol)
+    e = to_global(o.xyz[o.nv:], (de[:, :3], de[:, 3]), tol)
+    return np.concatenate([v, e])

@@ -197,7 +197,7 @@ int main( int argc, char** argv )
       if ( p != std::string::npos )
          a.kv[s.substr( 0, p )] = s.substr( p + 1 );
    }
-   if ( a.cmd.rfind( "p2", 0 ) == 0 )
+   if ( a.cmd.rfind( "p2", 0 ) == 0 || a.cmd == "shellmap" )
       return mainP2( a );
 
    const uint_t L    = uint_t( a.num( "level", 3 ) );

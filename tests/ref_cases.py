@@ -49,3 +49,30 @@ def gmg_start(o, L):
 
 def rel(a, b):
     return np.abs(a - b).max() / max(np.abs(b).max(), 1e-300)
+
+
+# ---- P2 elementwise path (tests/golden/ref_p2.npz, oracle/make_ref_fixtures_p2.py) ---------------------------------------------------
+GOLD_P2 = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_p2.npz")
+SHELL = (3, 2, 0.5, 1.0)
+BARY = np.array([[0.25, 0.25, 0.25, 0.25], [0.7, 0.1, 0.1, 0.1], [0.1, 0.6, 0.2, 0.1], [0.05, 0.15, 0.3, 0.5], [1, 0, 0, 0]])
+
+
+def gold_p2():
+    if "g2" not in _cache:
+        _cache["g2"] = np.load(GOLD_P2)
+    return _cache["g2"]
+
+
+def p2_oracle(kind, L):
+    from oracle import p2_oracle as p2
+    key = ("p2", kind, L)
+    if key not in _cache:
+        v, c = meshes.spherical_shell(*SHELL) if kind == "shell" else meshes.cube_6el()
+        _cache[key] = p2.P2Oracle(v, c, L, shell=(kind == "shell"))
+    return _cache[key]
+
+
+def p2_inputs(n, seed):
+    """same generator as oracle/make_ref_fixtures_p2.py: p2_inputs()"""
+    rng = np.random.default_rng(seed)
+    return rng.random(n) - 0.3, rng.random(n)
