@@ -292,3 +292,126 @@ class GeometricMultigridSolver(Solver):
         super().__init__(storage.lib, storage.lib.dll.hb_solver_create_gmg(
             storage.h, smoother.h, coarse_solver.h, min_level, max_level, pre, post, increment, cycle),
             (storage, smoother, coarse_solver))
+
+
+# ---- P2 function space, blending, fused elementwise operators (BASELINE configs 3 / 4) ------------------------------------------------
+
+def setIcosahedralShellMap(storage):
+    """IcosahedralShellMap::setMap( setupStorage ) (geometry/IcosahedralShellMap.hpp:491-510)"""
+    storage.lib.check(storage.lib.dll.hb_storage_set_icosahedral_shell_map(storage.h))
+
+
+def shellMapParameters(storage, local_cell):
+    out = np.zeros(14)
+    storage.lib.check(storage.lib.dll.hb_storage_shell_map_parameters(storage.h, local_cell, as_dp(out)))
+    return out
+
+
+def evalMap(storage, level, local_cell, x):
+    """GeometryMap::evalF / evalDF of a macro-cell at points x[n,3]: (F [n,3], DF [n,3,3])"""
+    x = f64(x).reshape(-1, 3)
+    out = np.zeros((len(x), 12))
+    storage.lib.check(storage.lib.dll.hb_storage_map_eval(storage.h, level, local_cell, as_dp(x), len(x), as_dp(out)))
+    return out[:, :3].copy(), out[:, 3:].reshape(-1, 3, 3).copy()
+
+
+class _VertexPart(P1Function):
+    """P2Function::getVertexDoFFunction(): a view on the P2 function's vertex DoFs (owned by the P2 function)"""
+
+    def __init__(self, p2, handle):
+        self.name, self.storage, self.lib = p2.name + "_v", p2.storage, p2.lib
+        self.min_level, self.max_level = p2.min_level, p2.max_level
+        self.h = handle
+        self._owner = p2
+
+    def __del__(self):
+        self.h = None
+
+
+class P2Function:
+    def __init__(self, name, storage, min_level, max_level):
+        self.name, self.storage, self.lib = name, storage, storage.lib
+        self.min_level, self.max_level = min_level, max_level
+        self.h = self.lib.checkp(self.lib.dll.hb_p2function_create(storage.h, min_level, max_level))
+        self.v = _VertexPart(self, self.lib.dll.hb_p2function_vertex_part(self.h))
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.lib.dll.hb_p2function_destroy(self.h)
+            self.h = None
+
+    def getVertexDoFFunction(self):
+        return self.v
+
+    def edge_size(self, level):
+        return self.storage.num_local_cells * int(self.lib.dll.hb_p2_edge_cell_size(level))
+
+    def upload(self, vertex_values, edge_values, level):
+        self.v.upload(vertex_values, level, All)
+        e = f64(edge_values).ravel()
+        assert e.size == self.edge_size(level), (e.size, self.edge_size(level))
+        self.lib.check(self.lib.dll.hb_p2function_upload_edges(self.h, level, as_dp(e)))
+
+    def download(self, level):
+        e = np.zeros(self.edge_size(level))
+        self.lib.check(self.lib.dll.hb_p2function_download_edges(self.h, level, as_dp(e)))
+        return self.v.download(level), e
+
+    def interpolate(self, value, level, flag=All):
+        self.lib.check(self.lib.dll.hb_p2function_interpolate_constant(self.h, float(value), level, flag))
+
+    def _lin(self, fn, scalars, functions, level, flag):
+        s = f64(scalars)
+        hs = (C.c_void_p * len(functions))(*[f.h for f in functions])
+        self.lib.check(fn(self.h, len(functions), as_dp(s), hs, level, flag))
+
+    def assign(self, scalars, functions, level, flag=All):
+        self._lin(self.lib.dll.hb_p2function_assign, scalars, functions, level, flag)
+
+    def add(self, scalars, functions, level, flag=All):
+        self._lin(self.lib.dll.hb_p2function_add, scalars, functions, level, flag)
+
+    def dotGlobal(self, other, level, flag=All):
+        out = C.c_double(0)
+        self.lib.check(self.lib.dll.hb_p2function_dot(self.h, other.h, level, flag, C.byref(out)))
+        return out.value
+
+
+class P2ElementwiseOperator:
+    """P2ElementwiseOperator< Form > (elementwiseoperators/P2ElementwiseOperator.hpp); k: P2Function, callable k(x, y, z) on
+    physical points (sampled at the quadrature points, the in-tree form's std::function), or None (k = 1)"""
+
+    def __init__(self, storage, min_level, max_level, handle, k):
+        self.storage, self.lib = storage, storage.lib
+        self.min_level, self.max_level = min_level, max_level
+        self.h = self.lib.checkp(handle)
+        self._k = k
+        if callable(k):
+            for L in range(min_level, max_level + 1):
+                n = int(self.lib.dll.hb_p2operator_num_quadrature_points(self.h, L))
+                xyz = np.zeros((n, 3))
+                self.lib.check(self.lib.dll.hb_p2operator_quadrature_points(self.h, L, as_dp(xyz)))
+                vals = f64(k(xyz[:, 0], xyz[:, 1], xyz[:, 2]) * np.ones(n))
+                self.lib.check(self.lib.dll.hb_p2operator_set_sampled_coefficient(self.h, L, as_dp(vals)))
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.lib.dll.hb_p2operator_destroy(self.h)
+            self.h = None
+
+    def apply(self, src, dst, level, flag, update=Replace):
+        self.lib.check(self.lib.dll.hb_p2operator_apply(self.h, src.h, dst.h, level, flag, update))
+
+
+class P2ElementwiseBlendingDivKGradOperator(P2ElementwiseOperator):
+    def __init__(self, storage, min_level, max_level, k=None):
+        kh = k.h if isinstance(k, P2Function) else None
+        super().__init__(storage, min_level, max_level, storage.lib.dll.hb_p2_divkgrad_create(storage.h, min_level, max_level, kh), k)
+
+
+class P2ElementwiseBlendingEpsilonBlock(P2ElementwiseOperator):
+    """block (i, j) of P2ElementwiseBlendingEpsilonOperator (elementwiseoperators/P2ElementwiseEpsilonOperator.hpp:112-170)"""
+
+    def __init__(self, storage, min_level, max_level, i, j, mu=None):
+        kh = mu.h if isinstance(mu, P2Function) else None
+        super().__init__(storage, min_level, max_level, storage.lib.dll.hb_p2_epsilon_create(storage.h, min_level, max_level, i, j, kh), mu)

@@ -90,6 +90,28 @@ _SIGNATURES = {
     "hb_p1_restrict": (C.c_int, [_vp, C.c_int, C.c_int]),
     "hb_p1_prolongate": (C.c_int, [_vp, C.c_int, C.c_int]),
     "hb_p1_prolongate_and_add": (C.c_int, [_vp, C.c_int, C.c_int]),
+    "hb_storage_set_icosahedral_shell_map": (C.c_int, [_vp]),
+    "hb_storage_shell_map_parameters": (C.c_int, [_vp, C.c_int, _dp]),
+    "hb_storage_map_eval": (C.c_int, [_vp, C.c_int, C.c_int, _dp, C.c_int, _dp]),
+    "hb_p2function_create": (_vp, [_vp, C.c_int, C.c_int]),
+    "hb_p2function_destroy": (None, [_vp]),
+    "hb_p2function_vertex_part": (_vp, [_vp]),
+    "hb_p2_edge_cell_size": (C.c_longlong, [C.c_int]),
+    "hb_p2function_upload_edges": (C.c_int, [_vp, C.c_int, _dp]),
+    "hb_p2function_download_edges": (C.c_int, [_vp, C.c_int, _dp]),
+    "hb_p2function_edge_device_ptr": (_vp, [_vp, C.c_int]),
+    "hb_p2_edge_endpoints": (C.c_int, [_vp, C.c_int, C.c_int, _dp]),
+    "hb_p2function_interpolate_constant": (C.c_int, [_vp, C.c_double, C.c_int, C.c_int]),
+    "hb_p2function_assign": (C.c_int, [_vp, C.c_int, _dp, C.POINTER(_vp), C.c_int, C.c_int]),
+    "hb_p2function_add": (C.c_int, [_vp, C.c_int, _dp, C.POINTER(_vp), C.c_int, C.c_int]),
+    "hb_p2function_dot": (C.c_int, [_vp, _vp, C.c_int, C.c_int, _dp]),
+    "hb_p2_divkgrad_create": (_vp, [_vp, C.c_int, C.c_int, _vp]),
+    "hb_p2_epsilon_create": (_vp, [_vp, C.c_int, C.c_int, C.c_int, C.c_int, _vp]),
+    "hb_p2operator_destroy": (None, [_vp]),
+    "hb_p2operator_num_quadrature_points": (C.c_longlong, [_vp, C.c_int]),
+    "hb_p2operator_quadrature_points": (C.c_int, [_vp, C.c_int, _dp]),
+    "hb_p2operator_set_sampled_coefficient": (C.c_int, [_vp, C.c_int, _dp]),
+    "hb_p2operator_apply": (C.c_int, [_vp, _vp, _vp, C.c_int, C.c_int, C.c_int]),
     "hb_solver_create_cg": (_vp, [_vp, C.c_int, C.c_int, C.c_int, C.c_double, C.c_double]),
     "hb_solver_create_weighted_jacobi": (_vp, [_vp, C.c_int, C.c_int, C.c_double]),
     "hb_solver_create_sor": (_vp, [C.c_double]),

@@ -1,0 +1,113 @@
+// P2 (vertexdof + edgedof) function storage and the fused on-the-fly elementwise operators: POD argument blocks and launchers.
+//
+// Layout contract (follows HyTeG): a P2 function on level L is a P1 function (vertex DoFs, hb_function) plus, per macro-cell, seven
+// edge-DoF arrays -- orientations X, Y, Z, XY, XZ, YZ as tetrahedral arrays of width N = 2^L and XYZ of width N - 1, one behind the other
+// (reference src/hyteg/edgedofspace/EdgeDoFIndexing.hpp:922-985, EdgeDoFOrientation.hpp:29-39).  Like the vertex arrays they cover the
+// CLOSED macro-tet: an edge DoF on a macro face / edge is stored in every adjacent macro-cell and all copies always hold the same value.
+#pragma once
+#include "hb_compat.h"
+#include "hb_types.h"
+
+#define HB_P2_MAXQ 11 // quadrature points of the largest rule (Xiao-Gimbutas 4)
+
+enum HbP2Form
+{
+   HB_P2_DIVKGRAD = 0, // int k grad(u) . grad(v), 11-point degree-4 rule (forms/form_hyteg_generated/p2/p2_div_k_grad_blending_q4.cpp)
+   HB_P2_EPSILON  = 1  // int 2 mu eps(phi_j e_d) : eps(phi_i e_c), 4-point degree-2 rule (p2_epsilonvar_blending_q2.cpp)
+};
+
+__host__ __device__ __forceinline__ int hb_p2_tet( int w )
+{
+   return ( w * ( w + 1 ) * ( w + 2 ) ) / 6;
+}
+// entries of one macro-cell's edge-DoF block
+__host__ __device__ __forceinline__ int hb_edge_cell_size( int N )
+{
+   return 6 * hb_p2_tet( N ) + hb_p2_tet( N - 1 );
+}
+// index inside a tetrahedral array of width w (entries x + y + z <= w - 1), reference indexing/MacroCellIndexing.hpp:44-52
+__host__ __device__ __forceinline__ int hb_tet_index( int w, int x, int y, int z )
+{
+   const int wz = w - z;
+   return hb_p2_tet( w ) - hb_p2_tet( wz ) + y * ( wz + 1 ) - ( y * ( y + 1 ) ) / 2 + x;
+}
+// edgedof::macrocell::index( level, x, y, z, orientation ), orientation 0..6 = X Y Z XY XZ YZ XYZ
+__host__ __device__ __forceinline__ int hb_edge_index( int N, int o, int x, int y, int z )
+{
+   return o * hb_p2_tet( N ) + hb_tet_index( o < 6 ? N : N - 1, x, y, z );
+}
+
+// everything the element kernel needs about one macro-cell: 4 vertices and the IcosahedralShellMap in derived form
+// F(x) = x r(x) / |x|,  r(x) = radRay + dr ( (x - ray) . n ) / volT      (reference geometry/IcosahedralShellMap.hpp:109-239)
+struct HbP2CellGeom
+{
+   double v[4][3];
+   double ray[3], n[3]; // n = (thr - ray) x (for - ray)
+   double radRay, drOverVolT;
+   int32_t bflag; // meshBoundaryFlag of the macro-cell
+   int32_t pad;
+};
+
+struct HbP2View
+{
+   int32_t           N, nCells;
+   int32_t           vCellSize, eCellSize; // entries per macro-cell: vertex array, edge block
+   int32_t           nAnchors;             // tet(N): logical micro-cell indices per type
+   int32_t           blending;             // 0 affine, 1 IcosahedralShellMap
+   const HbBndPoint* anchors;              // [nAnchors] (x,y,z) of the anchor, mask unused
+   const uint8_t*    vmask;                // [vCellSize] boundary mask of a vertex entry (HbLevelView::mask)
+   const uint8_t*    emask;                // [eCellSize] boundary mask of an edge entry = AND of its end points' masks
+   const HbCellInfo* cells;                // region tables (bflag / owner per mask)
+   const HbP2CellGeom* geom;               // [nCells]
+};
+
+struct HbP2ElemArgs
+{
+   const double* srcV;
+   const double* srcE;
+   double*       accV; // zeroed accumulators, same layout as the function
+   double*       accE;
+   const double* kV;   // coefficient as a P2 function (or null)
+   const double* kE;
+   const double* kq;   // coefficient sampled at the quadrature points [cell][type][anchor][q] (or null; null and no kV: k = 1)
+   int32_t       form, compC, compD;
+   int32_t       pad;
+};
+
+struct HbP2FinalizeArgs
+{
+   double*       dstV;
+   double*       dstE;
+   const double* accV;
+   const double* accE;
+   double        beta; // dst = beta * dst + acc on selected DoFs
+   uint32_t      selMask;
+   int32_t       pad;
+   const long long* grpStart; // interface groups: copies of one DoF, entry = arena offset (bit 62: edge arena)
+   const long long* grpEntry;
+   const uint8_t*   grpFlag;  // meshBoundaryFlag of the group's primitive
+   long long        nGroups;
+};
+
+// dst = sum_k c[k] src[k] (+ dst) on the edge DoFs selected by flag; also constants (n = 0, shift)
+struct HbP2LinComb
+{
+   double*       dst;
+   const double* src[4];
+   double        c[4];
+   double        shift;
+   int32_t       n, accumulate;
+   uint32_t      selMask;
+   int32_t       pad;
+};
+
+void hb_p2_launch_elements( const HbP2View& pv, const HbP2ElemArgs& a, cudaStream_t st );
+void hb_p2_launch_finalize( const HbP2View& pv, const HbP2FinalizeArgs& a, cudaStream_t st );
+void hb_p2_launch_edge_lincomb( const HbP2View& pv, const HbP2LinComb& lc, cudaStream_t st );
+// partial[blocks] <- sum over OWNED selected edge entries of a*b; returns the number of blocks used
+int hb_p2_launch_edge_dot( const HbP2View& pv, uint32_t selMask, const double* a, const double* b, double* partial, int maxBlocks, cudaStream_t st );
+// physical positions of the quadrature points [cell][type][anchor][q][3] (so that a host callback can be sampled there)
+void hb_p2_launch_quad_points( const HbP2View& pv, int form, double* out, cudaStream_t st );
+// F(x) and DF(x) of the cell's map at n points given in computational coordinates: out[n][12]
+void hb_p2_launch_map_eval( const HbP2View& pv, int cell, const double* x, int n, double* out, cudaStream_t st );
+int  hb_p2_num_quad_points( int form );

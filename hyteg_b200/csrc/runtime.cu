@@ -5,6 +5,7 @@
 #include <cstring>
 
 #include "../../include/hyteg_b200.h"
+#include "p2_kernels.h"
 #include "stencil_assembly.hpp"
 
 namespace hb {
@@ -487,8 +488,10 @@ hb_storage* hb_storage_create( int nV, const double* xyz, int nC, const int* cel
    HB_CATCH( nullptr )
 }
 
+void hb_p2_storage_released( hb_storage* st ); // runtime_p2.inc
 void hb_storage_destroy( hb_storage* st )
 {
+   hb_p2_storage_released( st );
    delete st;
 }
 
@@ -639,3 +642,4 @@ int hb_storage_micro_coordinates( const hb_storage* cst, int level, double* xyz 
 #include "runtime_comm.inc"
 #include "runtime_function.inc"
 #include "runtime_operator.inc"
+#include "runtime_p2.inc"

@@ -195,6 +195,51 @@ int        hb_solver_solve( hb_solver* s, hb_operator* op, hb_function* x, hb_fu
 int        hb_solver_iterations( const hb_solver* s );
 void       hb_solver_destroy( hb_solver* s );
 
+/* ==== P2 function space, geometry blending and the fused elementwise operators (BASELINE configs 3 and 4) ============================
+ * One rank only.  Data layout: the vertex DoFs are a P1Function (hb_p2function_vertex_part: all hb_p1function_* calls apply); the edge
+ * DoFs of a macro-cell are HyTeG's seven orientation arrays X Y Z XY XZ YZ (width 2^L) and XYZ (width 2^L - 1) one behind the other
+ * (src/hyteg/edgedofspace/EdgeDoFIndexing.hpp:922-985), macro-cell after macro-cell, covering the closed macro-tet. */
+typedef struct hb_p2function hb_p2function; /* P2Function<double>  (src/hyteg/p2functionspace/P2Function.hpp)                         */
+typedef struct hb_p2operator hb_p2operator; /* P2ElementwiseOperator<Form> (src/hyteg/elementwiseoperators/P2ElementwiseOperator.hpp)  */
+
+/* IcosahedralShellMap::setMap( setupStorage ) (src/hyteg/geometry/IcosahedralShellMap.hpp:491-510): every macro-cell gets the shell map
+ * of its prism (classifyVertices, :608-732).  Call before creating P2 operators. */
+int hb_storage_set_icosahedral_shell_map( hb_storage* st );
+/* rayVertex, refVertex, thrVertex, forVertex (3 doubles each), radRefVertex, radRayVertex of a macro-cell's map (:512-518) */
+int hb_storage_shell_map_parameters( hb_storage* st, int local_cell, double* out14 );
+/* GeometryMap::evalF / evalDF (:109-147, :169-239) on the device at n points x[n][3] of the macro-cell: out[n][12] = F (3), DF (9, row-major) */
+int hb_storage_map_eval( hb_storage* st, int level, int local_cell, const double* x, int n, double* out );
+
+hb_p2function* hb_p2function_create( hb_storage* st, int min_level, int max_level );
+void           hb_p2function_destroy( hb_p2function* f );
+hb_function*   hb_p2function_vertex_part( hb_p2function* f ); /* P2Function::getVertexDoFFunction(); owned by f */
+long long      hb_p2_edge_cell_size( int level );             /* entries of one macro-cell's edge block */
+int            hb_p2function_upload_edges( hb_p2function* f, int level, const double* host );   /* P2Function::getEdgeDoFFunction() data */
+int            hb_p2function_download_edges( const hb_p2function* f, int level, double* host );
+double*        hb_p2function_edge_device_ptr( hb_p2function* f, int level );
+/* computational coordinates of the two end points of every entry of a macro-cell's edge block: xyz[entries][2][3] */
+int hb_p2_edge_endpoints( hb_storage* st, int level, int local_cell, double* xyz );
+/* P2Function::interpolate( constant ) / assign / add / dotGlobal (src/hyteg/p2functionspace/P2Function.cpp) */
+int hb_p2function_interpolate_constant( hb_p2function* f, double value, int level, int flag );
+int hb_p2function_assign( hb_p2function* dst, int n, const double* scalars, hb_p2function* const* srcs, int level, int flag );
+int hb_p2function_add( hb_p2function* dst, int n, const double* scalars, hb_p2function* const* srcs, int level, int flag );
+int hb_p2function_dot( const hb_p2function* a, const hb_p2function* b, int level, int flag, double* out );
+
+/* P2ElementwiseOperator< forms::p2_div_k_grad_blending_q4 > (P2ElementwiseBlendingDivKGradOperator, P2ElementwiseOperator.hpp:475) /
+ * operatorgeneration::P2ElementwiseDivKGrad...: k as a P2Function (the hyteg_operators way; null: k = 1), or sampled at the quadrature
+ * points from a host callback (the in-tree form's std::function): hb_p2operator_quadrature_points tells where, in the order
+ * [macro-cell][micro-cell type][micro-cell index][quadrature point]; entries of micro-cells that do not exist are (0,0,0) / ignored. */
+hb_p2operator* hb_p2_divkgrad_create( hb_storage* st, int min_level, int max_level, const hb_p2function* k );
+/* P2ElementwiseOperator< forms::p2_epsilonvar_i_j_blending_q2 >: block (i, j) of P2ElementwiseBlendingEpsilonOperator
+ * (src/hyteg/elementwiseoperators/P2ElementwiseEpsilonOperator.hpp:112-170), viscosity mu like k above */
+hb_p2operator* hb_p2_epsilon_create( hb_storage* st, int min_level, int max_level, int i, int j, const hb_p2function* mu );
+void           hb_p2operator_destroy( hb_p2operator* op );
+long long      hb_p2operator_num_quadrature_points( hb_p2operator* op, int level );
+int            hb_p2operator_quadrature_points( hb_p2operator* op, int level, double* xyz ); /* physical (blended) positions */
+int            hb_p2operator_set_sampled_coefficient( hb_p2operator* op, int level, const double* values );
+/* Operator::apply( src, dst, level, flag, updateType ) -- P2ElementwiseOperator::gemv (P2ElementwiseOperator.cpp:109-330) */
+int hb_p2operator_apply( hb_p2operator* op, const hb_p2function* src, hb_p2function* dst, int level, int flag, int update_type );
+
 #ifdef __cplusplus
 }
 #endif

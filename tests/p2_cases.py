@@ -1,0 +1,106 @@
+"""P2 parity cases shared by the GPU tests (product CUDA library) and the CPU host-logic tests (test-only emulation build): the C-ABI
+path against tests/golden/ref_p2.npz (outputs of the reference itself) and against oracle/p2_oracle.py."""
+import numpy as np
+
+from hyteg_b200 import api, meshes
+from hyteg_b200.capi import Add, All, Inner, Replace
+from oracle import p2_oracle as p2
+import ref_cases as rc
+
+TOL = 1e-12
+
+
+class P2Setup:
+    def __init__(self, lib, kind, L):
+        self.o = rc.p2_oracle(kind, L)
+        v, c = (meshes.spherical_shell(*rc.SHELL) if kind == "shell" else meshes.cube_6el())
+        self.st = api.PrimitiveStorage(v, c, lib=lib)
+        self.st.setMeshBoundaryFlagsOnBoundary(1, 0, True)
+        if kind == "shell":
+            api.setIcosahedralShellMap(self.st)
+        self.L = L
+
+    def fn(self, name, x=None):
+        f = api.P2Function(name, self.st, self.L, self.L)
+        if x is not None:
+            v, e = self.o.to_cells(x)
+            f.upload(v, e, self.L)
+        return f
+
+    def get(self, f, tol=0.0):
+        v, e = f.download(self.L)
+        return self.o.from_cells(v, e, tol=tol)
+
+
+def k_xyz(x, y, z):
+    return p2.coefficient_k(np.stack([x, y, z], axis=-1))
+
+
+def case_shell_map(lib):
+    """device evalF / evalDF and the host classification against the reference's IcosahedralShellMap samples"""
+    from scipy.spatial import cKDTree
+    for nt, nr in ((3, 2), (2, 3)):
+        g = rc.gold_p2()["shellmap_%d_%d" % (nt, nr)]
+        v, c = meshes.spherical_shell(nt, nr, 0.5, 1.0)
+        st = api.PrimitiveStorage(v, c, lib=lib)
+        api.setIcosahedralShellMap(st)
+        tree = cKDTree(np.array([v[t].mean(0) for t in c]))
+        for row in g[:: max(1, len(g) // 60)]:
+            X = row[:12].reshape(4, 3)
+            d, ci = tree.query(X.mean(0))
+            F, DF = api.evalMap(st, 1, int(ci), rc.BARY @ X)
+            for k in range(5):
+                assert np.abs(F[k] - row[12 + 12 * k:15 + 12 * k]).max() < 1e-14
+                assert np.abs(DF[k] - row[15 + 12 * k:24 + 12 * k].reshape(3, 3)).max() < 1e-13
+
+
+def case_divkgrad(lib, kind, L, mode="sampled"):
+    """P2ElementwiseBlendingDivKGradOperator::apply against the reference's output (k through the callback path) and, with k as a
+    P2 function (the hyteg_operators interface), against the oracle"""
+    g = rc.gold_p2()
+    s = P2Setup(lib, kind, L)
+    x, d0 = rc.p2_inputs(s.o.n, 300 + L)
+    src, dst = s.fn("src", x), s.fn("dst", d0)
+    if mode == "sampled":
+        A = api.P2ElementwiseBlendingDivKGradOperator(s.st, L, L, k_xyz)
+        A.apply(src, dst, L, Inner, Replace)
+        name = ("shell_L%d_divkgrad_inner" if kind == "shell" else "cube_6el_L%d_divkgrad_inner") % L
+        assert rc.rel(s.get(dst, tol=1e-13), g[name]) < TOL
+        if kind == "shell" and L == 2:
+            dst = s.fn("dst", d0)
+            A.apply(src, dst, L, All, Add)
+            assert rc.rel(s.get(dst, tol=1e-13), g["shell_L2_divkgrad_add_all"]) < TOL
+    else:
+        kvec = p2.coefficient_k(s.o.dof_physical_coordinates())
+        kf = s.fn("k", kvec)
+        A = api.P2ElementwiseBlendingDivKGradOperator(s.st, L, L, kf)
+        A.apply(src, dst, L, Inner, Replace)
+        want = p2.apply(s.o, s.o.matrix(form="divkgrad", kvec=kvec), x, d0, Inner)
+        assert rc.rel(s.get(dst, tol=1e-13), want) < TOL
+
+
+def case_epsilon(lib, i, j):
+    g = rc.gold_p2()
+    s = P2Setup(lib, "shell", 2)
+    x, d0 = rc.p2_inputs(s.o.n, 302)
+    src, dst = s.fn("src", x), s.fn("dst", d0)
+    A = api.P2ElementwiseBlendingEpsilonBlock(s.st, 2, 2, i, j, k_xyz)
+    A.apply(src, dst, 2, Inner, Replace)
+    assert rc.rel(s.get(dst, tol=1e-13), g["shell_L2_epsilon_%d%d_inner" % (i, j)]) < TOL
+
+
+def case_blas(lib):
+    s = P2Setup(lib, "shell", 2)
+    a, b = rc.p2_inputs(s.o.n, 7)
+    fa, fb, fc = s.fn("a", a), s.fn("b", b), s.fn("c")
+    for flag in (All, Inner):
+        m = s.o.mask(flag)
+        assert abs(fa.dotGlobal(fb, 2, flag) - a[m] @ b[m]) < 1e-11 * abs(a[m] @ b[m])
+    fc.interpolate(0.5, 2, All)
+    fc.assign([2.0, -3.0], [fa, fb], 2, Inner)
+    want = np.full(s.o.n, 0.5)
+    m = s.o.mask(Inner)
+    want[m] = 2 * a[m] - 3 * b[m]
+    assert rc.rel(s.get(fc), want) < 1e-15
+    fc.add([0.25], [fa], 2, All)
+    assert rc.rel(s.get(fc), want + 0.25 * a) < 1e-15
