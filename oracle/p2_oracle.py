@@ -340,3 +340,27 @@ def apply(o, M, x, dst, flag, add=False):
     out = dst.copy()
     out[m] = (out[m] + y[m]) if add else y[m]
     return out
+
+
+# ---- quadratic grid transfer ---------------------------------------------------------------------------------------------------------
+
+def quadratic_prolongation(coarse, fine, tol=1e-9):
+    """P2toP2QuadraticProlongation as a matrix [fine.n, coarse.n]: nodal interpolation -- the coarse P2 function evaluated at every fine
+    DoF position (reference src/hyteg/gridtransferoperators/P2toP2QuadraticProlongation.cpp, generated prolongate_3D_macrocell_P2_push_*).
+    P2toP2QuadraticRestriction (P2toP2QuadraticRestriction.cpp:131-251) is its transpose."""
+    from scipy.spatial import cKDTree
+    lat = np.array([(i, j, k, 4 - i - j - k) for i in range(5) for j in range(5 - i) for k in range(5 - i - j)], dtype=np.float64) / 4.0
+    shapes = np.array([p2_shape(l)[0] for l in lat])  # [35,10]
+    tree = cKDTree(fine.xyz)
+    X = np.einsum("pk,eki->epi", lat, coarse.el_X)  # [ne,35,3]
+    d, idx = tree.query(X.reshape(-1, 3))
+    assert d.max() < tol, d.max()
+    rows = np.repeat(idx, 10)
+    cols = np.repeat(coarse.el_dofs, 35, axis=0).ravel()
+    vals = np.tile(shapes, (len(coarse.el_X), 1)).ravel()
+    # every (fine, coarse) pair appears once per coarse element containing the fine point, always with the same value: keep one
+    key = rows * coarse.n + cols
+    _, first = np.unique(key, return_index=True)
+    P = sp.csr_matrix((vals[first], (rows[first], cols[first])), shape=(fine.n, coarse.n))
+    P.eliminate_zeros()
+    return P
