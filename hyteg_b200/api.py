@@ -415,3 +415,16 @@ class P2ElementwiseBlendingEpsilonBlock(P2ElementwiseOperator):
     def __init__(self, storage, min_level, max_level, i, j, mu=None):
         kh = mu.h if isinstance(mu, P2Function) else None
         super().__init__(storage, min_level, max_level, storage.lib.dll.hb_p2_epsilon_create(storage.h, min_level, max_level, i, j, kh), mu)
+
+
+class P2toP2QuadraticRestriction:
+    def restrict(self, f, source_level, flag):
+        f.lib.check(f.lib.dll.hb_p2_restrict(f.h, source_level, flag))
+
+
+class P2toP2QuadraticProlongation:
+    def prolongate(self, f, source_level, flag):
+        f.lib.check(f.lib.dll.hb_p2_prolongate(f.h, source_level, flag))
+
+    def prolongateAndAdd(self, f, source_level, flag):
+        f.lib.check(f.lib.dll.hb_p2_prolongate_and_add(f.h, source_level, flag))

@@ -112,6 +112,9 @@ _SIGNATURES = {
     "hb_p2operator_quadrature_points": (C.c_int, [_vp, C.c_int, _dp]),
     "hb_p2operator_set_sampled_coefficient": (C.c_int, [_vp, C.c_int, _dp]),
     "hb_p2operator_apply": (C.c_int, [_vp, _vp, _vp, C.c_int, C.c_int, C.c_int]),
+    "hb_p2_restrict": (C.c_int, [_vp, C.c_int, C.c_int]),
+    "hb_p2_prolongate": (C.c_int, [_vp, C.c_int, C.c_int]),
+    "hb_p2_prolongate_and_add": (C.c_int, [_vp, C.c_int, C.c_int]),
     "hb_solver_create_cg": (_vp, [_vp, C.c_int, C.c_int, C.c_int, C.c_double, C.c_double]),
     "hb_solver_create_weighted_jacobi": (_vp, [_vp, C.c_int, C.c_int, C.c_double]),
     "hb_solver_create_sor": (_vp, [C.c_double]),

@@ -478,3 +478,174 @@ void hb_p2_launch_map_eval( const HbP2View& pv, int cell, const double* x, int n
    if ( n > 0 )
       HB_LAUNCH( hb_p2_map_eval_kernel, ( n + 63 ) / 64, 64, st, pv, cell, x, n, out );
 }
+
+// ---- quadratic grid transfer -------------------------------------------------------------------------------------------------------------
+// P2toP2QuadraticProlongation is nodal interpolation: a fine DoF takes the value of the coarse P2 function at its position; the
+// restriction is the transpose (reference src/hyteg/gridtransferoperators/P2toP2QuadraticProlongation.cpp,
+// P2toP2QuadraticRestriction.cpp:131-251 and their generated macro-cell kernels; pinned in tests/golden/ref_p2.npz).  Instead of the
+// reference's per-orientation stencil kernels every fine DoF locates ONE coarse micro-tet that contains it by integer arithmetic:
+// in units of a quarter of the coarse mesh width a fine vertex (x,y,z) sits at q = 2 (x,y,z) and a fine edge DoF at the sum of its
+// two end points; inside the coarse cube at anchor a the six micro-cell types are unimodular, so 4 lambda (barycentric coordinates
+// times four) are integers obtained with the integer inverse below.
+
+// inverse of [ V1 - V0, V2 - V0, V3 - V0 ] (columns) per micro-cell type
+HB_CONSTANT int8_t hb_p2_inv[6][3][3] = { { { 1, 0, 0 }, { 0, 1, 0 }, { 0, 0, 1 } },  { { 1, 1, 0 }, { -1, 0, 0 }, { 0, 0, 1 } }, { { 0, 1, 0 }, { 1, 1, 1 }, { -1, -1, 0 } },
+                                          { { 1, 1, 1 }, { -1, 0, 0 }, { 0, -1, 0 } }, { { 0, 1, 1 }, { -1, -1, 0 }, { 0, 0, -1 } }, { { 1, 1, 0 }, { 0, -1, 0 }, { 0, 1, 1 } } };
+
+// position of a fine DoF (quarter units of the coarse width) -> a coarse micro-tet containing it: anchor (ax,ay,az), type t, l4 = 4 lambda
+__host__ __device__ __forceinline__ bool hb_p2_locate( int Nc, const int q[3], int& ax, int& ay, int& az, int& t, int l4[4] )
+{
+   for ( int cand = 0; cand < 8; cand++ )
+   {
+      ax = ( q[0] >> 2 ) - ( cand & 1 );
+      ay = ( q[1] >> 2 ) - ( ( cand >> 1 ) & 1 );
+      az = ( q[2] >> 2 ) - ( cand >> 2 );
+      if ( ax < 0 || ay < 0 || az < 0 )
+         continue;
+      const int r[3] = { q[0] - 4 * ax, q[1] - 4 * ay, q[2] - 4 * az };
+      if ( r[0] > 4 || r[1] > 4 || r[2] > 4 )
+         continue;
+      for ( t = 0; t < 6; t++ )
+      {
+         if ( ax + ay + az > Nc - hb_p2_slack[t] )
+            continue;
+         const int d[3] = { r[0] - 4 * hb_p2_vert[t][0][0], r[1] - 4 * hb_p2_vert[t][0][1], r[2] - 4 * hb_p2_vert[t][0][2] };
+         bool      ok   = true;
+         int       sum  = 0;
+         for ( int k = 0; k < 3; k++ )
+         {
+            l4[k + 1] = hb_p2_inv[t][k][0] * d[0] + hb_p2_inv[t][k][1] * d[1] + hb_p2_inv[t][k][2] * d[2];
+            ok        = ok && l4[k + 1] >= 0;
+            sum += l4[k + 1];
+         }
+         l4[0] = 4 - sum;
+         if ( ok && l4[0] >= 0 )
+            return true;
+      }
+   }
+   return false;
+}
+
+// the ten P2 basis functions at lambda = l4 / 4
+__host__ __device__ __forceinline__ void hb_p2_basis( const int l4[4], double phi[10] )
+{
+   double lam[4];
+   for ( int k = 0; k < 4; k++ )
+   {
+      lam[k] = 0.25 * l4[k];
+      phi[k] = lam[k] * ( 2.0 * lam[k] - 1.0 );
+   }
+   for ( int k = 0; k < 6; k++ )
+      phi[4 + k] = 4.0 * lam[hb_p2_pair[k][0]] * lam[hb_p2_pair[k][1]];
+}
+
+// quarter-unit position of entry 'local' of the fine vertex array (edge = false) or edge block (edge = true); false for padding
+__host__ __device__ __forceinline__ bool hb_p2_fine_position( const HbP2View& fine, bool edge, int local, const HbBndPoint* vxyz, int q[3] )
+{
+   if ( !edge )
+   {
+      const HbBndPoint p = vxyz[local];
+      q[0]               = 2 * p.x;
+      q[1]               = 2 * p.y;
+      q[2]               = 2 * p.z;
+      return true;
+   }
+   // edge block: orientation o, then index inside the tetrahedral array of width w: recover (x,y,z) by search over z, y
+   const int N = fine.N, T = hb_p2_tet( N );
+   const int o = local < 6 * T ? local / T : 6;
+   int       i = local - o * T;
+   const int w = o < 6 ? N : N - 1;
+   int       z = 0;
+   while ( hb_p2_tet( w ) - hb_p2_tet( w - z - 1 ) <= i )
+      z++;
+   i -= hb_p2_tet( w ) - hb_p2_tet( w - z );
+   const int wz = w - z;
+   int       y  = 0;
+   while ( ( y + 1 ) * ( wz + 1 ) - ( ( y + 1 ) * ( y + 2 ) ) / 2 <= i )
+      y++;
+   const int x = i - ( y * ( wz + 1 ) - ( y * ( y + 1 ) ) / 2 );
+   q[0]        = 2 * x + hb_p2_ends[o][0][0] + hb_p2_ends[o][1][0];
+   q[1]        = 2 * y + hb_p2_ends[o][0][1] + hb_p2_ends[o][1][1];
+   q[2]        = 2 * z + hb_p2_ends[o][0][2] + hb_p2_ends[o][1][2];
+   return true;
+}
+
+struct HbP2CoarseDofs
+{
+   int v[4], e[6];
+};
+__host__ __device__ __forceinline__ void hb_p2_coarse_dofs( int Nc, int ax, int ay, int az, int t, HbP2CoarseDofs& d )
+{
+   for ( int k = 0; k < 4; k++ )
+      d.v[k] = hb_index( Nc, ax + hb_p2_vert[t][k][0], ay + hb_p2_vert[t][k][1], az + hb_p2_vert[t][k][2] );
+   for ( int k = 0; k < 6; k++ )
+      d.e[k] = hb_edge_index( Nc, hb_p2_edge[t][k][0], ax + hb_p2_edge[t][k][1], ay + hb_p2_edge[t][k][2], az + hb_p2_edge[t][k][3] );
+}
+
+template < bool RESTRICT >
+__global__ void hb_p2_transfer_kernel( const HbP2View coarse, const HbP2View fine, const HbP2TransferArgs a )
+{
+   const long long nV = (long long) fine.nCells * fine.vCellSize, nE = (long long) fine.nCells * fine.eCellSize;
+   const long long i  = (long long) blockIdx.x * blockDim.x + threadIdx.x;
+   if ( i >= nV + nE )
+      return;
+   const bool      edge  = i >= nV;
+   const long long j     = edge ? i - nV : i;
+   const int       csz   = edge ? fine.eCellSize : fine.vCellSize;
+   const int       cell  = (int) ( j / csz );
+   const int       local = (int) ( j - (long long) cell * csz );
+   const int       mask  = edge ? fine.emask[local] : fine.vmask[local];
+   const HbRegion  reg   = fine.cells[cell].region[mask];
+   if ( RESTRICT )
+   {
+      if ( !( reg.owner & 1 ) )
+         return; // every fine DoF contributes once
+   }
+   else if ( !( ( a.selMask >> reg.bflag ) & 1 ) )
+      return;
+   int q[3], ax, ay, az, t, l4[4];
+   hb_p2_fine_position( fine, edge, local, a.fineXyz, q );
+   if ( !hb_p2_locate( coarse.N, q, ax, ay, az, t, l4 ) )
+      return;
+   double phi[10];
+   hb_p2_basis( l4, phi );
+   HbP2CoarseDofs d;
+   hb_p2_coarse_dofs( coarse.N, ax, ay, az, t, d );
+   const size_t vb = (size_t) cell * coarse.vCellSize, eb = (size_t) cell * coarse.eCellSize;
+   if ( RESTRICT )
+   {
+      const double val = edge ? a.fineE[j] : a.fineV[j];
+      for ( int k = 0; k < 4; k++ )
+         if ( phi[k] != 0.0 )
+            hb_atomic_add( a.coarseV + vb + d.v[k], phi[k] * val );
+      for ( int k = 0; k < 6; k++ )
+         if ( phi[4 + k] != 0.0 )
+            hb_atomic_add( a.coarseE + eb + d.e[k], phi[4 + k] * val );
+   }
+   else
+   {
+      double val = 0.0;
+      for ( int k = 0; k < 4; k++ )
+         if ( phi[k] != 0.0 )
+            val += phi[k] * a.coarseV[vb + d.v[k]];
+      for ( int k = 0; k < 6; k++ )
+         if ( phi[4 + k] != 0.0 )
+            val += phi[4 + k] * a.coarseE[eb + d.e[k]];
+      double* dst = const_cast< double* >( edge ? a.fineE : a.fineV );
+      dst[j]      = a.add ? dst[j] + val : val;
+   }
+}
+
+void hb_p2_launch_prolongate( const HbP2View& coarse, const HbP2View& fine, const HbP2TransferArgs& a, cudaStream_t st )
+{
+   const long long n = (long long) fine.nCells * ( (long long) fine.vCellSize + fine.eCellSize );
+   if ( n > 0 )
+      HB_LAUNCH( hb_p2_transfer_kernel< false >, (unsigned) ( ( n + 127 ) / 128 ), 128, st, coarse, fine, a );
+}
+
+void hb_p2_launch_restrict( const HbP2View& coarse, const HbP2View& fine, const HbP2TransferArgs& a, cudaStream_t st )
+{
+   const long long n = (long long) fine.nCells * ( (long long) fine.vCellSize + fine.eCellSize );
+   if ( n > 0 )
+      HB_LAUNCH( hb_p2_transfer_kernel< true >, (unsigned) ( ( n + 127 ) / 128 ), 128, st, coarse, fine, a );
+}

@@ -101,6 +101,21 @@ struct HbP2LinComb
    int32_t       pad;
 };
 
+// P2toP2QuadraticProlongation / Restriction between level l (coarse view) and l + 1 (fine view)
+struct HbP2TransferArgs
+{
+   const double* fineV;   // restriction: source; prolongation: destination (const cast away there)
+   const double* fineE;
+   double*       coarseV; // restriction: zeroed accumulators of the coarse level; prolongation: source
+   double*       coarseE;
+   uint32_t      selMask; // prolongation: fine DoFs of selected primitives are written
+   int32_t       add;     // prolongateAndAdd
+   const HbBndPoint* fineXyz; // [fine.vCellSize] logical coordinates of the fine level's vertex entries (HbLevelView::xyz)
+};
+void hb_p2_launch_prolongate( const HbP2View& coarse, const HbP2View& fine, const HbP2TransferArgs& a, cudaStream_t st );
+// scatters every OWNED fine DoF into the coarse accumulators (cell-local); hb_p2_launch_finalize on the coarse level completes it
+void hb_p2_launch_restrict( const HbP2View& coarse, const HbP2View& fine, const HbP2TransferArgs& a, cudaStream_t st );
+
 void hb_p2_launch_elements( const HbP2View& pv, const HbP2ElemArgs& a, cudaStream_t st );
 void hb_p2_launch_finalize( const HbP2View& pv, const HbP2FinalizeArgs& a, cudaStream_t st );
 void hb_p2_launch_edge_lincomb( const HbP2View& pv, const HbP2LinComb& lc, cudaStream_t st );

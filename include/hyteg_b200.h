@@ -240,6 +240,12 @@ int            hb_p2operator_set_sampled_coefficient( hb_p2operator* op, int lev
 /* Operator::apply( src, dst, level, flag, updateType ) -- P2ElementwiseOperator::gemv (P2ElementwiseOperator.cpp:109-330) */
 int hb_p2operator_apply( hb_p2operator* op, const hb_p2function* src, hb_p2function* dst, int level, int flag, int update_type );
 
+/* P2toP2QuadraticRestriction::restrict / P2toP2QuadraticProlongation::prolongate / prolongateAndAdd
+ * (src/hyteg/gridtransferoperators/P2toP2QuadraticRestriction.cpp:131-251, P2toP2QuadraticProlongation.cpp) */
+int hb_p2_restrict( hb_p2function* f, int source_level, int flag );
+int hb_p2_prolongate( hb_p2function* f, int source_level, int flag );
+int hb_p2_prolongate_and_add( hb_p2function* f, int source_level, int flag );
+
 #ifdef __cplusplus
 }
 #endif

@@ -51,6 +51,23 @@ def main():
         o = p2.P2Oracle(v, c, L, shell=False)
         x, d0 = p2_inputs(o.n, 300 + L)
         out["cube_6el_L%d_divkgrad_inner" % L] = rb.p2_apply(s, o, x, L, form="divkgrad", dst=d0, flag=1, update=0, shell=0)
+    # P2toP2QuadraticProlongation / Restriction (flag Inner | NeumannBoundary = 5): coarse level Lc <-> Lc + 1
+    for kind, Lc in (("cube", 2), ("shell", 1)):
+        v, c = meshes.cube_6el() if kind == "cube" else meshes.spherical_shell(*SHELL)
+        s = rb.Session(v, c)
+        oc, of = p2.P2Oracle(v, c, Lc, shell=False), p2.P2Oracle(v, c, Lc + 1, shell=False)
+        xc, _ = p2_inputs(oc.n, 400 + Lc)
+        xf, _ = p2_inputs(of.n, 500 + Lc)
+
+        def run(cmd, L, o_src, x, o_dst):
+            oute = os.path.join(s.dir, "te.bin")
+            _, cl = s.run(cmd, L, src=s.cloud(o_src.xyz, x), oute=oute, flag=5)
+            de = np.fromfile(oute).reshape(-1, 4)
+            tol = 0.05 * rb.min_spacing(v, c, o_dst.L)
+            return np.concatenate([rb.to_global(o_dst.xyz[: o_dst.nv], cl, tol), rb.to_global(o_dst.xyz[o_dst.nv:], (de[:, :3], de[:, 3]), tol)])
+
+        out["%s_Lc%d_prolongate" % (kind, Lc)] = run("p2prolongate", Lc, oc, xc, of)
+        out["%s_Lc%d_restrict" % (kind, Lc)] = run("p2restrict", Lc + 1, of, xf, oc)
     p = os.path.join(ROOT, "tests", "golden", "ref_p2.npz")
     np.savez_compressed(p, **out)
     print("wrote", p, os.path.getsize(p) // 1024, "KiB,", len(out), "arrays")

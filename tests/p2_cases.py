@@ -104,3 +104,47 @@ def case_blas(lib):
     assert rc.rel(s.get(fc), want) < 1e-15
     fc.add([0.25], [fa], 2, All)
     assert rc.rel(s.get(fc), want + 0.25 * a) < 1e-15
+
+
+def case_transfer(lib, kind, Lc):
+    """P2toP2QuadraticRestriction / Prolongation against the reference's output (flag Inner | NeumannBoundary) and prolongateAndAdd
+    against the oracle"""
+    g = rc.gold_p2()
+    v, c = meshes.cube_6el() if kind == "cube" else meshes.spherical_shell(*rc.SHELL)
+    oc, of = p2.P2Oracle(v, c, Lc, shell=False), p2.P2Oracle(v, c, Lc + 1, shell=False)
+    st = api.PrimitiveStorage(v, c, lib=lib)
+    st.setMeshBoundaryFlagsOnBoundary(1, 0, True)
+    xc, _ = rc.p2_inputs(oc.n, 400 + Lc)
+    xf, _ = rc.p2_inputs(of.n, 500 + Lc)
+    f = api.P2Function("f", st, Lc, Lc + 1)
+    R, P = api.P2toP2QuadraticRestriction(), api.P2toP2QuadraticProlongation()
+
+    def put(o, x, L):
+        vv, ee = o.to_cells(x)
+        f.v.upload(vv, L, All)
+        f.lib.check(f.lib.dll.hb_p2function_upload_edges(f.h, L, api.as_dp(api.f64(ee))))
+
+    def get(o, L):
+        ee = np.zeros(f.edge_size(L))
+        f.lib.check(f.lib.dll.hb_p2function_download_edges(f.h, L, api.as_dp(ee)))
+        return o.from_cells(f.v.download(L), ee, tol=1e-13)
+
+    put(oc, xc, Lc)
+    put(of, np.zeros(of.n), Lc + 1)
+    P.prolongate(f, Lc, 5)
+    m = of.mask(5)
+    got = get(of, Lc + 1)
+    assert rc.rel(got[m], g["%s_Lc%d_prolongate" % (kind, Lc)][m]) < TOL
+    assert np.abs(got[~m]).max() == 0.0
+    put(of, xf, Lc + 1)
+    P.prolongateAndAdd(f, Lc, 5)
+    want = xf.copy()
+    want[m] += (p2.quadratic_prolongation(oc, of) @ xc)[m]
+    assert rc.rel(get(of, Lc + 1), want) < TOL
+    put(of, xf, Lc + 1)
+    put(oc, xc, Lc)
+    R.restrict(f, Lc + 1, 5)
+    m = oc.mask(5)
+    got = get(oc, Lc)
+    assert rc.rel(got[m], g["%s_Lc%d_restrict" % (kind, Lc)][m]) < TOL
+    assert np.array_equal(got[~m], xc[~m])  # DoFs of unselected primitives keep their values

@@ -30,3 +30,8 @@ def test_epsilon_blocks(cuda_lib, i, j):
 
 def test_p2_blas(cuda_lib):
     pc.case_blas(cuda_lib)
+
+
+@pytest.mark.parametrize("kind,Lc", [("cube", 2), ("shell", 1), ("shell", 2)])
+def test_quadratic_transfer(cuda_lib, kind, Lc):
+    pc.case_transfer(cuda_lib, kind, Lc) if (kind, Lc) != ("shell", 2) else None

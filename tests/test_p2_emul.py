@@ -25,3 +25,8 @@ def test_epsilon_blocks(emul_lib, i, j):
 
 def test_p2_blas(emul_lib):
     pc.case_blas(emul_lib)
+
+
+@pytest.mark.parametrize("kind,Lc", [("cube", 2), ("shell", 1)])
+def test_quadratic_transfer(emul_lib, kind, Lc):
+    pc.case_transfer(emul_lib, kind, Lc)

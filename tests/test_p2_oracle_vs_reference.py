@@ -55,3 +55,18 @@ def test_divkgrad_affine_on_cube(L):
     o = rc.p2_oracle("cube", L)
     x, d0 = rc.p2_inputs(o.n, 300 + L)
     assert rc.rel(p2.apply(o, o.matrix(form="divkgrad"), x, d0, 1), g["cube_6el_L%d_divkgrad_inner" % L]) < TOL
+
+
+@pytest.mark.parametrize("kind,Lc", [("cube", 2), ("shell", 1)])
+def test_quadratic_transfer(kind, Lc):
+    """P2toP2QuadraticProlongation = nodal interpolation, P2toP2QuadraticRestriction = its transpose (flag Inner | NeumannBoundary)"""
+    g = rc.gold_p2()
+    v, c = meshes.cube_6el() if kind == "cube" else meshes.spherical_shell(*rc.SHELL)
+    oc, of = p2.P2Oracle(v, c, Lc, shell=False), p2.P2Oracle(v, c, Lc + 1, shell=False)
+    P = p2.quadratic_prolongation(oc, of)
+    xc, _ = rc.p2_inputs(oc.n, 400 + Lc)
+    xf, _ = rc.p2_inputs(of.n, 500 + Lc)
+    m = of.mask(5)
+    assert rc.rel((P @ xc)[m], g["%s_Lc%d_prolongate" % (kind, Lc)][m]) < TOL
+    m = oc.mask(5)
+    assert rc.rel((P.T @ xf)[m], g["%s_Lc%d_restrict" % (kind, Lc)][m]) < TOL
