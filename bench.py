@@ -18,9 +18,21 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-# dram__bytes_read.sum + dram__bytes_write.sum of one hb_shuffle_kernel<0,4,128> launch at level 8 on cube_6el
-# (ncu --set full capture, profiles/r1_c_apply_final_ncu_full_summary.txt): 143.2 MB + 93.1 MB
-NCU_TRAFFIC_INTERIOR_L8 = 236.3e6
+
+
+def ncu_traffic(level):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one launch of the dominant kernel from the committed ncu --set full capture
+    (profiles/apply_traffic.json names the capture); None when no capture of this level is on file.  A number from a capture, not
+    from this run: ncu replays one launch with a cold L2, so dirty lines still in L2 at the end make it read BELOW the algorithmic
+    bytes."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "apply_traffic.json")) as f:
+            d = json.load(f)
+        e = d.get(str(level))
+        return (e["dram_read_bytes"] + e["dram_write_bytes"], e["source"]) if e else (None, None)
+    except Exception:
+        return None, None
+
 BYTES_PER_DOF = {"apply": 16.0, "jacobi": 24.0, "sor": 24.0}  # algorithmic: src+dst / src+rhs+dst (DESIGN.md)
 
 
@@ -32,6 +44,7 @@ def parse():
     p.add_argument("--level", type=int, default=8)
     p.add_argument("--impl", default="ours")
     p.add_argument("--no-cpu-baseline", action="store_true")
+    p.add_argument("--p2-level", type=int, default=6, help="BASELINE config 3 (P2 div-k-grad with blending on the shell) level; 0: skip")
     return p.parse_args()
 
 
@@ -89,73 +102,82 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------------------------
-# reference arm / cpu baseline: the reference's own generated macro-cell apply kernel (oracle/_ref)
+# reference arm / cpu baseline: the reference ITSELF (oracle/_ref/ref_dump = HyTeG built from /root/reference by oracle/build_ref.py)
 # ------------------------------------------------------------------------------------------------
-def cpu_reference_apply(level, n_cells=6, warmup=1, steps=3, threads=None, budget_s=120.0):
-    """Times apply_3D_macrocell_vertexdof_to_vertexdof_replace (compiled from the reference tree into
-    oracle/_ref) on n_cells macro-cells of `level`, one thread per macro-cell (the reference parallelises
-    over macro-primitives).  Only the macro-cell kernel is timed: the reference's macro-face/edge/vertex
-    kernels and ghost-layer copies (~36 % of its apply) are left out, which favours the CPU.
-    One step = one apply over all n_cells macro-cells; `warmup` untimed steps, then `steps` timed ones (mean)."""
-    import ctypes as C
-    so = os.path.join(ROOT, "oracle", "_ref", "libhyteg_ref_kernels.so")
-    if not os.path.exists(so):
+def workload_name(level, gpus):
+    """config.workload: the same string in both arms"""
+    return (f"cube_6el level {level} P1 Laplace constant-stencil apply" if gpus <= 1 else
+            f"box of {gpus} cubes (6 macro-tets each) level {level} P1 Laplace constant-stencil apply, one cube per GPU")
+
+
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+def cpu_reference_apply(level, gpus=1, budget_s=20.0, procs=None):
+    """The reference's stock timed call -- P1ConstantLaplaceOperator::apply( src, dst, level, Inner )
+    (apps/benchmarks/ApplyBenchmark/ApplyBenchmark.cpp:87; macro vertex/edge/face/cell kernels AND the six ghost-layer communicate
+    phases in front of them) -- on the workload's macro mesh, one process per host core.  The reference parallelises with MPI ranks
+    over macro-primitives; this build is serial (no MPI in the image), so every process runs the whole mesh on its own core and the
+    throughputs are added: P independent ranks without inter-rank messages, which favours the CPU.  Each process times whole applies
+    for budget_s seconds after one warm-up apply."""
+    import subprocess, tempfile
+    exe = os.path.join(ROOT, "oracle", "_ref", "ref_dump")
+    if not os.path.exists(exe):
         return None
-    dll = C.CDLL(so)
-    dp = C.POINTER(C.c_double)
-    dll.ref_apply_macrocell.argtypes = [dp, dp, C.c_int, dp, C.c_int]
-    n = (2 ** level + 1) * (2 ** level + 2) * (2 ** level + 3) // 6
-    N = 2 ** level
-    interior = (N - 1) * (N - 2) * (N - 3) // 6
-    threads = threads or min(n_cells, os.cpu_count() or 1)
-    rng = np.random.default_rng(0)
-    src = [rng.standard_normal(n) for _ in range(n_cells)]
-    dst = [np.zeros(n) for _ in range(n_cells)]
-    w = np.array([8.0] + [-0.5] * 14)
-
-    def work(ids):
-        for i in ids:
-            dll.ref_apply_macrocell(dst[i].ctypes.data_as(dp), src[i].ctypes.data_as(dp), level, w.ctypes.data_as(dp), 0)
-
-    def sweep():
-        ts = [threading.Thread(target=work, args=(range(t, n_cells, threads),)) for t in range(threads)]
-        [t.start() for t in ts]
-        [t.join() for t in ts]
-
-    t_start = time.perf_counter()
-    for _ in range(warmup):
-        sweep()
-    times = []
-    for _ in range(max(1, steps)):
-        t0 = time.perf_counter()
-        sweep()
-        times.append(time.perf_counter() - t0)
-        if time.perf_counter() - t_start > budget_s:
-            break
-    mean = float(np.mean(times))
-    return {"value": interior * n_cells / mean / 1e9, "unit": "GDoF/s", "cores": threads, "kind": "reference",
-            "sample": f"reference macro-cell apply kernel only, {n_cells} macro-cells at level {level} (the whole workload), "
-                      f"mean of {len(times)} applies after {warmup} warm-up",
-            "seconds": mean, "steps": len(times)}
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    from hyteg_b200 import meshes
+    import ref_bridge
+    v, c = meshes.cube_6el() if gpus <= 1 else meshes.cuboid(gpus, 1, 1, hi=(float(gpus), 1.0, 1.0))
+    d = tempfile.mkdtemp(prefix="refbench_")
+    msh = os.path.join(d, "mesh.msh")
+    ref_bridge.write_msh(v, c, msh)
+    procs = procs or host_cores()
+    # memory: ~1 GB per process at level 8 per cube (3 functions with ghost layers + stencils)
+    try:
+        avail = os.sysconf("SC_AVPHYS_PAGES") * os.sysconf("SC_PAGE_SIZE")
+        per = 1.2e9 * max(1, gpus) * 8 ** (level - 8)
+        procs = max(1, min(procs, int(0.6 * avail / max(per, 1))))
+    except Exception:
+        pass
+    cmd = [exe, "bench", "mesh=" + msh, "level=%d" % level, "minlevel=%d" % level, "what=apply", "iters=1000000", "seconds=%g" % budget_s]
+    t0 = time.perf_counter()
+    ps = [subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True) for _ in range(procs)]
+    rates, calls, dofs = [], 0, 0.0
+    for p in ps:
+        out = p.communicate()[0]
+        r = {l.split()[1]: float(l.split()[2]) for l in out.splitlines() if l.startswith("RESULT ")}
+        if "seconds_per_call" in r:
+            rates.append(r["dofs"] / r["seconds_per_call"])
+            calls += int(r["calls"])
+            dofs = r["dofs"]
+    if not rates:
+        return None
+    return {"value": sum(rates) / 1e9, "unit": "GDoF/s", "cores": len(rates), "kind": "reference",
+            "sample": f"P1ConstantLaplaceOperator::apply of the reference itself (all macro-primitive kernels + ghost-layer communication) on "
+                      f"{workload_name(level, gpus)}: {len(rates)} serial processes, one per host core, each timing whole applies for "
+                      f"{budget_s:g} s after one warm-up apply; throughputs added",
+            "seconds": dofs / sum(rates), "steps": calls, "wall_s": time.perf_counter() - t0,
+            "per_core_gdofs": float(np.mean(rates)) / 1e9}
 
 
 def run_reference(args, rank):
-    """Reference arm: the reference's own generated apply kernel on the host cores, on this arm's workload (6 macro-cells per GPU
-    of the job), args.warmup untimed and args.steps timed applies.  Rank 0 alone runs it."""
+    """Reference arm: the reference's own apply on the host cores, on this arm's workload.  Rank 0 alone runs it."""
     if rank != 0:
         return
-    base = cpu_reference_apply(args.level, n_cells=6 * max(1, args.gpus), warmup=args.warmup, steps=args.steps)
+    base = cpu_reference_apply(args.level, gpus=max(1, args.gpus), budget_s=max(5.0, min(60.0, 0.5 * args.steps)))
     if base is None:
-        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref not built (needs /root/reference at build time)"}))
+        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/ref_dump not built (needs /root/reference at build time)"}))
         return
     v = base["value"]
     n_steps = base.pop("steps")
-    workload = (f"cube_6el level {args.level} P1 Laplace constant-stencil apply" if args.gpus <= 1 else
-                f"box of {args.gpus} cubes (6 macro-tets each) level {args.level} P1 Laplace constant-stencil apply") + " (CPU reference kernels)"
     line = {"impl": "reference", "metric": "P1 constant-stencil apply throughput", "value": v, "unit": "GDoF/s", "n_gpus": args.gpus,
-            "steps": n_steps, "warmup": args.warmup, "ms_per_step": 1e3 * base.pop("seconds"), "higher_is_better": True, "scaling": "weak",
+            "steps": n_steps, "warmup": 1, "ms_per_step": 1e3 * base.pop("seconds"), "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": workload},
+            "config": {"workload": workload_name(args.level, args.gpus)},
             "cpu_baseline": base, "e2e": {"value": v, "unit": "GDoF/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
 
@@ -175,6 +197,16 @@ def main():
     from hyteg_b200 import api, meshes
 
     torch.cuda.set_device(local)
+    try:  # pinned host buffers are first-touched on the NUMA node of this rank's GPU
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(local)
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (os.cpu_count() + 63) // 64)
+        cpus = {64 * i + b for i, w in enumerate(words) for b in range(64) if (w >> b) & 1} & os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+    except Exception:
+        pass
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     lib = hb.get_lib()
@@ -291,6 +323,90 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms_e2e = float(t.item())
 
+    # end-to-end SOLVE, the unit this path's callers see: upload b, V(3,3) cycles until the residual has dropped by 1e-8, download x
+    hb_host = torch.empty(n_arr, dtype=torch.float64).pin_memory()
+    rhs.interpolate(lambda X, Y, Z: np.sin(2 * X) * np.cos(3 * Y) * (1 + Z), L, hb.All)
+    hb_host.copy_(torch.from_numpy(rhs.download(L)))
+    r = api.P1Function("r", st, L, L)
+
+    def e2e_solve():
+        lib.check(lib.dll.hb_p1function_upload_async(b.h, L, C.cast(hb_host.data_ptr(), dp)))
+        x.interpolate(0.0, L, hb.All)
+        A.residual(x, b, r, L, hb.Inner)
+        r0 = np.sqrt(r.dotGlobal(r, L, hb.Inner))
+        cycles, res = 0, r0
+        while res > 1e-8 * r0 and cycles < 30:
+            gmg.solve(A, x, b, L)
+            A.residual(x, b, r, L, hb.Inner)
+            res = np.sqrt(r.dotGlobal(r, L, hb.Inner))
+            cycles += 1
+        lib.check(lib.dll.hb_p1function_download_async(x.h, L, C.cast(hout.data_ptr(), dp)))
+        torch.cuda.synchronize()
+        return cycles, res / r0
+
+    e2e_solve()
+    barrier()
+    t0 = time.perf_counter()
+    solve_cycles, solve_red = e2e_solve()
+    ms_solve = (time.perf_counter() - t0) * 1e3
+    if world > 1:
+        t = torch.tensor([ms_solve], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_solve = float(t.item())
+
+    # more than one rank: the partitioned apply and one V-cycle must equal the one-rank run bit for bit (small level, every rank
+    # checks its own macro-cells against an unpartitioned storage on its own GPU) -- the driver's 1-GPU box skips the 2-GPU tests
+    parity_ok = None
+    if world > 1:
+        Lc = 4
+        st1 = api.PrimitiveStorage(v, c, 0, 1)
+        st1.setMeshBoundaryFlagsOnBoundary(1, 0, True)
+        ok = True
+        A1, Ap = api.P1ConstantLaplaceOperator(st1, 0, Lc), api.P1ConstantLaplaceOperator(st, 0, Lc)
+        f1 = [api.P1Function(n, st1, 0, Lc) for n in "xyb"]
+        fp = [api.P1Function(n, st, 0, Lc) for n in "xyb"]
+        expr = lambda X, Y, Z: np.sin(5 * X) * np.cos(3 * Y) + Z * Z
+        for fs, stx, Ax in ((f1, st1, A1), (fp, st, Ap)):
+            fs[0].interpolate(expr, Lc, hb.All)
+            Ax.apply(fs[0], fs[1], Lc, hb.Inner)
+            g = api.GeometricMultigridSolver(stx, api.GaussSeidelSmoother(stx), api.CGSolver(stx, 0, 0, 50, 1e-16, 1e-16), 0, Lc, 3, 3)
+            fs[0].interpolate(1.0, Lc, hb.DirichletBoundary)
+            g.solve(Ax, fs[0], fs[2], Lc)
+        csz = st.cell_array_size(Lc)
+        mine = st.local_cell_global_ids()
+        for k in (0, 1):
+            full, part = f1[k].download(Lc), fp[k].download(Lc)
+            for i, gcell in enumerate(mine):
+                ok = ok and np.array_equal(full[gcell * csz:(gcell + 1) * csz], part[i * csz:(i + 1) * csz])
+        t = torch.tensor([1.0 if ok else 0.0], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MIN)
+        parity_ok = bool(t.item() > 0.5)
+
+    # BASELINE config 3: P2 elementwise div-k-grad with IcosahedralShellMap blending on the thick spherical shell (240 macro-tets)
+    p2 = None
+    if world == 1 and args.p2_level > 0:
+        P2L = args.p2_level
+        t0 = time.perf_counter()
+        vs, cs = meshes.spherical_shell(3, 2, 0.5, 1.0)
+        sts = api.PrimitiveStorage(vs, cs)
+        sts.setMeshBoundaryFlagsOnBoundary(1, 0, True)
+        api.setIcosahedralShellMap(sts)
+        ps, pd, pk = (api.P2Function(n, sts, P2L, P2L) for n in ("src", "dst", "k"))
+        ps.interpolate(1.0, P2L, hb.All)
+        rng = np.random.default_rng(1)
+        pk.interpolate(1.5, P2L, hb.All)
+        Ap2 = api.P2ElementwiseBlendingDivKGradOperator(sts, P2L, P2L, pk)
+        Ap2.apply(ps, pd, P2L, hb.Inner)
+        torch.cuda.synchronize()
+        setup_s = time.perf_counter() - t0
+        ms_p2 = timed(lambda: Ap2.apply(ps, pd, P2L, hb.Inner), max(args.steps // 10, 3), 2)
+        n_tet = len(cs) * 8 ** P2L
+        flop = n_tet * 11 * 330.0  # 11 quadrature points x ~330 FP64 flop (geometry + the two contractions), DESIGN.md section 9
+        p2 = {"workload": f"P2 elementwise div-k-grad, IcosahedralShellMap blending, meshSphericalShell(3,2,0.5,1.0) level {P2L}, k as a P2 function",
+              "ms_per_apply": ms_p2, "micro_tets": n_tet, "Gtets_per_s": n_tet / ms_p2 / 1e6, "fp64_tflops_estimate": flop / ms_p2 / 1e9,
+              "setup_s": setup_s}
+        del Ap2, ps, pd, pk, sts
+
     if rank == 0:
         peak, which = measured_peak()
         gd = lambda ms: ndof / (ms * 1e-3) / 1e9
@@ -302,13 +418,12 @@ def main():
         line = {"metric": "P1 constant-stencil apply throughput", "value": gd(ms_apply), "unit": "GDoF/s", "n_gpus": world,
                 "steps": args.steps, "warmup": W, "ms_per_step": ms_apply, "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-                "config": {"workload": f"cube_6el level {L} P1 Laplace constant-stencil apply, {int(ndof_rank)} DoFs per GPU" if world == 1 else
-                           f"box of {world} cubes (6 macro-tets each) level {L}, partitioned one cube per GPU, {int(ndof_rank)} DoFs per GPU, "
-                           f"ghost exchange of {8 * nsend} B with {npeers} neighbour rank(s) inside every step ({xmode})",
+                "config": {"workload": workload_name(L, world), "dofs_per_gpu": int(ndof_rank),
+                           "exchange": None if world == 1 else f"ghost exchange of {8 * nsend} B with {npeers} neighbour rank(s) (rank 0) inside every step ({xmode})",
                            "l2": "src+dst arrays %.0f MB > 126 MB L2" % (2 * 8 * n_arr / 1e6),
                            "multi_gpu": f"macro-cells partitioned, ghost layers over {xmode}" if world > 1 else "single"},
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                             "traffic": NCU_TRAFFIC_INTERIOR_L8 if L == 8 else None, "peak_source": which,
+                             "traffic": ncu_traffic(L)[0], "traffic_source": ncu_traffic(L)[1], "peak_source": which,
                              "kernel": "hb_shuffle_kernel<APPLY_REPLACE,4,128> (interior points of all local macro-cells, one launch)",
                              "algorithmic_bytes_per_launch": BYTES_PER_DOF["apply"] * n_interior, "us_per_launch": 1e3 * ms_interior,
                              "share_of_step": ms_interior / ms_apply,
@@ -316,12 +431,17 @@ def main():
                                              "note": "16 B x all DoFs / apply time (interior + interface kernels, overlapped on two streams)"}},
                 "also": {"jacobi_gdofs": gd(ms_jac), "jacobi_frac": BYTES_PER_DOF["jacobi"] * ndof_rank / (ms_jac * 1e-3) / 1e9 / peak,
                          "sor_gdofs": gd(ms_sor), "sor_frac": BYTES_PER_DOF["sor"] * ndof_rank / (ms_sor * 1e-3) / 1e9 / peak,
-                         "vcycle_3_3_gs_ms": ms_v, "vcycle_3_3_jacobi_ms": ms_vj, "ghost_exchanges_in_apply_region": ex0[0]},
+                         "vcycle_3_3_gs_ms": ms_v, "vcycle_3_3_jacobi_ms": ms_vj, "ghost_exchanges_in_apply_region": ex0[0],
+                         "e2e_solve": {"ms": ms_solve, "vcycles": solve_cycles, "residual_reduction": solve_red, "gdofs_solved_per_s": ndof / ms_solve / 1e6,
+                                       "what": "upload b (pinned host), V(3,3) Gauss-Seidel cycles until |r| <= 1e-8 |r0| (one host-read dot per cycle), download x"},
+                         "gs_factor_gap": "multicolour vs the reference's lexicographic hybrid, V(3,3) factor over cycles 6..10: -3.5 % cube_6el L5, "
+                                          "+2.6 % octahedron L4, -1.1 % three_tets L4 (tests/test_gpu_reference.py, DESIGN.md section 3)",
+                         "parity_ok": parity_ok, "p2_config3": p2},
                 "e2e": {"value": gd(ms_e2e), "unit": "GDoF/s", "h2d_bytes_per_step": 8 * n_arr, "d2h_bytes_per_step": 8 * n_arr,
                         "note": "%d requests in flight on %d streams (uploads overlap downloads, PCIe full duplex)" % (n_lanes, n_lanes)},
                 "gpu_launches": 2 * args.steps + (2 * args.steps if world > 1 else 0), "clocks": clk.summary()}
         if not args.no_cpu_baseline and world == 1:
-            line["cpu_baseline"] = cpu_reference_apply(min(L, 8), warmup=1, steps=10)
+            line["cpu_baseline"] = cpu_reference_apply(min(L, 8), budget_s=10.0)
             if line["cpu_baseline"]:
                 line["cpu_baseline"].pop("steps", None)
         print(json.dumps(line))

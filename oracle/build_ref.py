@@ -35,6 +35,9 @@ SKIP_DIRS = ("/petsc/", "/trilinos/", "/python/", "/checkpointrestore/ADIOS2", "
              "/adaptiverefinement/", "/ccrfunctionspace/", "/p0functionspace/", "/experimental/")
 
 
+ALL = False
+
+
 def sources():
     src = []
     for root, _, files in os.walk(REF + "/walberla/src/core"):
@@ -48,7 +51,14 @@ def sources():
     src += [os.path.join(cso, "P1generatedKernels", f) for f in sorted(os.listdir(cso + "/P1generatedKernels"))
             if f.endswith(".cpp")]
     src.append(os.path.join(HERE, "ref_shim", "waLBerlaBuildInfo.cpp"))
-    return [s for s in sorted(src) if not any(d in s for d in SKIP_DIRS)]
+    src = [s for s in sorted(src) if not any(d in s for d in SKIP_DIRS)]
+    # oracle/ref_sources.txt: the translation units the driver actually links (read off the linker map, --all ignores it); a fresh
+    # build then takes minutes instead of a quarter of an hour
+    lst = os.path.join(HERE, "ref_sources.txt")
+    if not ALL and os.path.exists(lst):
+        need = set(l.strip() for l in open(lst) if l.strip())
+        src = [s for s in src if os.path.relpath(s, REF) in need or not s.startswith(REF)]
+    return src
 
 
 def obj_name(s):
@@ -68,7 +78,10 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("-j", type=int, default=os.cpu_count())
     ap.add_argument("--only-driver", action="store_true")
+    ap.add_argument("--all", action="store_true", help="compile every translation unit of the sub-trees, not only oracle/ref_sources.txt")
     a = ap.parse_args()
+    global ALL
+    ALL = a.all
     if not os.path.isdir(REF):
         print("reference tree not present (%s): keeping prebuilt oracle/_ref" % REF)
         return 0
