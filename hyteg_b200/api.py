@@ -18,12 +18,19 @@ SMOOTH_FLAG = Inner | NeumannBoundary | FreeslipBoundary
 class PrimitiveStorage:
     """SetupPrimitiveStorage + PrimitiveStorage for tetrahedral macro meshes."""
 
-    def __init__(self, vertices, cells, rank=0, n_ranks=1, lib=None):
+    def __init__(self, vertices, cells, rank=0, n_ranks=1, lib=None, cell_rank=None):
+        """cell_rank: target rank of every macro-cell (e.g. meshes.partition_greedy); None: contiguous blocks"""
         self.lib = lib or capi.get_lib()
         self.vertices = f64(vertices).reshape(-1, 3)
         self.cells = i32(cells).reshape(-1, 4)
-        self.h = self.lib.checkp(self.lib.dll.hb_storage_create(
-            len(self.vertices), as_dp(self.vertices), len(self.cells), as_ip(self.cells), rank, n_ranks))
+        if cell_rank is None:
+            self.h = self.lib.checkp(self.lib.dll.hb_storage_create(
+                len(self.vertices), as_dp(self.vertices), len(self.cells), as_ip(self.cells), rank, n_ranks))
+        else:
+            cr = i32(cell_rank)
+            assert len(cr) == len(self.cells)
+            self.h = self.lib.checkp(self.lib.dll.hb_storage_create_partitioned(
+                len(self.vertices), as_dp(self.vertices), len(self.cells), as_ip(self.cells), rank, n_ranks, as_ip(cr)))
         self.rank, self.n_ranks = rank, n_ranks
 
     def __del__(self):

@@ -43,6 +43,7 @@ _SIGNATURES = {
     "hb_storage_exchange_info": (C.c_int, [_vp, C.c_int, _ip, C.POINTER(C.c_longlong), C.POINTER(C.c_longlong)]),
     "hb_p1function_communicate": (C.c_int, [_vp, C.c_int]),
     "hb_storage_create": (_vp, [C.c_int, _dp, C.c_int, _ip, C.c_int, C.c_int]),
+    "hb_storage_create_partitioned": (_vp, [C.c_int, _dp, C.c_int, _ip, C.c_int, C.c_int, _ip]),
     "hb_storage_destroy": (None, [_vp]),
     "hb_storage_set_mesh_boundary_flags_on_boundary": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int]),
     "hb_storage_counts": (C.c_int, [_vp, _ip]),

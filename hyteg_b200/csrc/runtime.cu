@@ -95,7 +95,7 @@ void hb_storage::uploadTopologyTables()
       kv.second->view.nSlots = (int) view.slotGlobal.size();
    }
    tablesDirty = false;
-   g_constOwner = nullptr; // macro-cell flags may have changed
+   g_constOwner = nullptr; // macro-cell flags may have changed (operators created afterwards stage the new flags)
 }
 
 void hb_storage::buildChunkDescs( hb::LevelTables& lt )
@@ -471,11 +471,22 @@ int hb_set_tuning( const char* key, int value )
 
 hb_storage* hb_storage_create( int nV, const double* xyz, int nC, const int* cells, int rank, int nRanks )
 {
+   return hb_storage_create_partitioned( nV, xyz, nC, cells, rank, nRanks, nullptr );
+}
+
+hb_storage* hb_storage_create_partitioned( int nV, const double* xyz, int nC, const int* cells, int rank, int nRanks, const int* cellRank )
+{
    HB_TRY
    require( nRanks >= 1 && rank >= 0 && rank < nRanks, "bad rank / n_ranks" );
    auto st = std::make_unique< hb_storage >();
    st->topo.build( nV, xyz, nC, cells );
    st->topo.partition( nRanks );
+   if ( cellRank )
+      for ( int c = 0; c < nC; c++ )
+      {
+         require( cellRank[c] >= 0 && cellRank[c] < nRanks, "cell_rank entry outside [0, n_ranks)" );
+         st->topo.cellRank[(size_t) c] = cellRank[c];
+      }
    st->view.rank   = rank;
    st->view.nRanks = nRanks;
    st->reducePartial.alloc( HB_REDUCE_MAX_BLOCKS );

@@ -137,8 +137,14 @@ struct hb_operator
    std::vector< hb::DeviceBuffer< double > > W;  // per level [nSlots][16][15]
    std::vector< std::vector< double > >      hW; // host copy
    const double* weights( int L ) const;
-   // interior weights of all levels in constant memory (shuffle kernel): entry of (level L, local cell c) = constBase(L) + c
-   bool constUsable() const;
-   int  constBase( int L ) const;
-   void ensureConstWeights();
+   // Interior weights in constant memory (shuffle kernel).  If (levels x local cells) fit the table, all levels are resident and the
+   // entry of (level L, local cell c) is constBase(L) + c; otherwise ONE level is resident at a time (entry c) and a launch on another
+   // level re-uploads it, stream-ordered from a pinned staging buffer (no host synchronisation).  More local cells than table
+   // entries: the shuffle kernel is not used (a one-time message says so).
+   bool    constUsable() const;
+   bool    constAllLevels() const;
+   int     constBase( int L ) const;
+   void    ensureConstWeights( int L );
+   double* stage = nullptr; // pinned: [levels][nLocal][16] weights, then [levels][nLocal] flags
+   ~hb_operator();
 };

@@ -124,3 +124,96 @@ def spherical_shell(ntan, nrad, rmin=0.5, rmax=1.0):
                 cells.append([l[0], l[1], h[1], h[2]])
                 cells.append([l[0], h[0], h[1], h[2]])
     return np.array(verts), np.array(cells, dtype=np.int32)
+
+
+def partition_greedy(cells, n_parts):
+    """Connected, equally sized blocks of macro-cells: n_parts regions grown breadth-first over the face-adjacency graph from seeds
+    spread over the mesh, one cell per region per round -- in the spirit of the reference's loadbalancing::greedy
+    (src/hyteg/primitivestorage/loadbalancing/SimpleBalancer.hpp:56-78).  Returns the target rank of every cell."""
+    from collections import deque
+    cells = np.asarray(cells)
+    n = len(cells)
+    if n_parts <= 1:
+        return np.zeros(n, dtype=np.int32)
+    face_cells = {}
+    for c, t in enumerate(cells):
+        for f in ((0, 1, 2), (0, 1, 3), (0, 2, 3), (1, 2, 3)):
+            face_cells.setdefault(tuple(sorted(int(t[i]) for i in f)), []).append(c)
+    adj = [[] for _ in range(n)]
+    for cs in face_cells.values():
+        if len(cs) == 2:
+            adj[cs[0]].append(cs[1])
+            adj[cs[1]].append(cs[0])
+
+    def bfs_dist(srcs):
+        d = np.full(n, -1)
+        q = deque(srcs)
+        for s in srcs:
+            d[s] = 0
+        while q:
+            u = q.popleft()
+            for w in adj[u]:
+                if d[w] < 0:
+                    d[w] = d[u] + 1
+                    q.append(w)
+        return d
+
+    seeds = [0]
+    for _ in range(1, n_parts):  # farthest-point seeding
+        d = bfs_dist(seeds)
+        seeds.append(int(np.argmax(np.where(d < 0, n, d))))
+    rank = np.full(n, -1, dtype=np.int32)
+    fronts = []
+    for r, s in enumerate(seeds):
+        rank[s] = r
+        fronts.append(deque([s]))
+    size = [1] * n_parts
+    target = [(n + n_parts - 1 - r) // n_parts for r in range(n_parts)]
+    left = n - n_parts
+    while left > 0:
+        progressed = False
+        for r in range(n_parts):
+            if size[r] >= target[r]:
+                continue
+            got = False
+            while fronts[r] and not got:
+                u = fronts[r][0]
+                for w in adj[u]:
+                    if rank[w] < 0:
+                        rank[w] = r
+                        fronts[r].append(w)
+                        size[r] += 1
+                        left -= 1
+                        got = progressed = True
+                        break
+                if not got:
+                    fronts[r].popleft()
+        if not progressed:  # enclosed leftovers: give them to the smallest neighbouring region
+            for c in np.nonzero(rank < 0)[0]:
+                nb = [rank[w] for w in adj[c] if rank[w] >= 0]
+                if nb:
+                    r = min(nb, key=lambda q: size[q])
+                    rank[c] = r
+                    size[r] += 1
+                    left -= 1
+            if left > 0 and not any(rank[w] >= 0 for c in np.nonzero(rank < 0)[0] for w in adj[c]):
+                rank[rank < 0] = int(np.argmin(size))
+                left = 0
+    # diffusion: hand boundary cells from larger to smaller neighbouring regions until the sizes differ by at most one
+    for _ in range(4 * n):
+        moved = False
+        for c in range(n):
+            a = rank[c]
+            best = None
+            for w in adj[c]:
+                b = rank[w]
+                if b != a and size[a] > size[b] + 1 and (best is None or size[b] < size[best]):
+                    best = b
+            if best is not None and sum(1 for w in adj[c] if rank[w] == a) >= 1:
+                rank[c] = best
+                size[a] -= 1
+                size[best] += 1
+                moved = True
+        if not moved or max(size) - min(size) <= 1:
+            break
+    return rank

@@ -88,6 +88,9 @@ int hb_set_tuning( const char* key, int value );
 /* cells: 4 vertex ids per macro-tet, in mesh order (MeshInfo).  Macro-cells are distributed over
  * n_ranks in contiguous blocks; this process keeps the cells of 'rank'. */
 hb_storage* hb_storage_create( int n_vertices, const double* xyz, int n_cells, const int* cells, int rank, int n_ranks );
+/* same with the target rank of every macro-cell given by the caller (SetupPrimitiveStorage::setTargetRank; what the load balancers of
+ * src/hyteg/primitivestorage/loadbalancing/SimpleBalancer.hpp:56-78 compute).  cell_rank == NULL: contiguous blocks. */
+hb_storage* hb_storage_create_partitioned( int n_vertices, const double* xyz, int n_cells, const int* cells, int rank, int n_ranks, const int* cell_rank );
 void        hb_storage_destroy( hb_storage* st );
 /* SetupPrimitiveStorage::setMeshBoundaryFlagsOnBoundary (SetupPrimitiveStorage.cpp:977-988) */
 int hb_storage_set_mesh_boundary_flags_on_boundary( hb_storage* st, int flag_on_boundary, int flag_inner, int highest_dim_always_inner );
