@@ -44,6 +44,7 @@ def parse():
     p.add_argument("--level", type=int, default=8)
     p.add_argument("--impl", default="ours")
     p.add_argument("--no-cpu-baseline", action="store_true")
+    p.add_argument("--mesh", default="auto", choices=["auto", "shell", "cubes"], help="auto: cube_6el on one GPU, the spherical shell on several")
     p.add_argument("--p2-level", type=int, default=6, help="BASELINE config 3 (P2 div-k-grad with blending on the shell) level; 0: skip")
     return p.parse_args()
 
@@ -104,10 +105,26 @@ class ClockSampler:
 # ------------------------------------------------------------------------------------------------
 # reference arm / cpu baseline: the reference ITSELF (oracle/_ref/ref_dump = HyTeG built from /root/reference by oracle/build_ref.py)
 # ------------------------------------------------------------------------------------------------
-def workload_name(level, gpus):
+def workload_mesh(gpus, mesh="auto"):
+    """macro mesh of the job: BASELINE configs[1] (cube_6el) on one GPU, configs[4] -- the icosahedral spherical shell with one radial
+    layer of 60 macro-tets per GPU (meshSphericalShell(2, gpus + 1, 0.5, 1.0)) -- on several"""
+    from hyteg_b200 import meshes
+    if mesh == "cubes":
+        return meshes.cuboid(gpus, 1, 1, hi=(float(gpus), 1.0, 1.0)), "cubes"
+    if gpus <= 1 and mesh != "shell":
+        return meshes.cube_6el(), "cube"
+    return meshes.spherical_shell(2, gpus + 1, 0.5, 1.0), "shell"
+
+
+def workload_name(level, gpus, mesh="auto"):
     """config.workload: the same string in both arms"""
-    return (f"cube_6el level {level} P1 Laplace constant-stencil apply" if gpus <= 1 else
-            f"box of {gpus} cubes (6 macro-tets each) level {level} P1 Laplace constant-stencil apply, one cube per GPU")
+    kind = "cubes" if mesh == "cubes" else ("cube" if gpus <= 1 and mesh != "shell" else "shell")
+    if kind == "cube":
+        return f"cube_6el level {level} P1 Laplace constant-stencil apply"
+    if kind == "cubes":
+        return f"box of {gpus} cubes (6 macro-tets each) level {level} P1 Laplace constant-stencil apply, one cube per GPU"
+    return (f"spherical shell meshSphericalShell(2,{gpus + 1},0.5,1.0) ({60 * gpus} macro-tets) level {level} P1 Laplace constant-stencil apply, "
+            f"macro-cells partitioned into {gpus} connected blocks of 60 (greedy balancer)")
 
 
 def host_cores():
@@ -117,7 +134,7 @@ def host_cores():
         return os.cpu_count() or 1
 
 
-def cpu_reference_apply(level, gpus=1, budget_s=20.0, procs=None):
+def cpu_reference_apply(level, gpus=1, budget_s=20.0, procs=None, mesh="auto"):
     """The reference's stock timed call -- P1ConstantLaplaceOperator::apply( src, dst, level, Inner )
     (apps/benchmarks/ApplyBenchmark/ApplyBenchmark.cpp:87; macro vertex/edge/face/cell kernels AND the six ghost-layer communicate
     phases in front of them) -- on the workload's macro mesh, one process per host core.  The reference parallelises with MPI ranks
@@ -131,7 +148,8 @@ def cpu_reference_apply(level, gpus=1, budget_s=20.0, procs=None):
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     from hyteg_b200 import meshes
     import ref_bridge
-    v, c = meshes.cube_6el() if gpus <= 1 else meshes.cuboid(gpus, 1, 1, hi=(float(gpus), 1.0, 1.0))
+    # several GPUs: every process runs ONE radial layer of the shell (60 macro-tets, the share of one GPU) -- a bounded sample of the job
+    (v, c), kind = workload_mesh(1 if mesh != "cubes" else gpus, "shell" if (gpus > 1 and mesh != "cubes") or mesh == "shell" else mesh)
     d = tempfile.mkdtemp(prefix="refbench_")
     msh = os.path.join(d, "mesh.msh")
     ref_bridge.write_msh(v, c, msh)
@@ -139,7 +157,7 @@ def cpu_reference_apply(level, gpus=1, budget_s=20.0, procs=None):
     # memory: ~1 GB per process at level 8 per cube (3 functions with ghost layers + stencils)
     try:
         avail = os.sysconf("SC_AVPHYS_PAGES") * os.sysconf("SC_PAGE_SIZE")
-        per = 1.2e9 * max(1, gpus) * 8 ** (level - 8)
+        per = 0.2e9 * len(c) * 8 ** (level - 8)
         procs = max(1, min(procs, int(0.6 * avail / max(per, 1))))
     except Exception:
         pass
@@ -158,7 +176,8 @@ def cpu_reference_apply(level, gpus=1, budget_s=20.0, procs=None):
         return None
     return {"value": sum(rates) / 1e9, "unit": "GDoF/s", "cores": len(rates), "kind": "reference",
             "sample": f"P1ConstantLaplaceOperator::apply of the reference itself (all macro-primitive kernels + ghost-layer communication) on "
-                      f"{workload_name(level, gpus)}: {len(rates)} serial processes, one per host core, each timing whole applies for "
+                      f"{workload_name(level, gpus, mesh)}" + (" -- every process runs the share of one GPU (one radial layer, 60 macro-tets)" if kind == "shell" and gpus > 1 else "") +
+                      f": {len(rates)} serial processes, one per host core, each timing whole applies for "
                       f"{budget_s:g} s after one warm-up apply; throughputs added",
             "seconds": dofs / sum(rates), "steps": calls, "wall_s": time.perf_counter() - t0,
             "per_core_gdofs": float(np.mean(rates)) / 1e9}
@@ -168,7 +187,7 @@ def run_reference(args, rank):
     """Reference arm: the reference's own apply on the host cores, on this arm's workload.  Rank 0 alone runs it."""
     if rank != 0:
         return
-    base = cpu_reference_apply(args.level, gpus=max(1, args.gpus), budget_s=max(5.0, min(60.0, 0.5 * args.steps)))
+    base = cpu_reference_apply(args.level, gpus=max(1, args.gpus), budget_s=max(5.0, min(60.0, 0.5 * args.steps)), mesh=args.mesh)
     if base is None:
         print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/ref_dump not built (needs /root/reference at build time)"}))
         return
@@ -177,7 +196,7 @@ def run_reference(args, rank):
     line = {"impl": "reference", "metric": "P1 constant-stencil apply throughput", "value": v, "unit": "GDoF/s", "n_gpus": args.gpus,
             "steps": n_steps, "warmup": 1, "ms_per_step": 1e3 * base.pop("seconds"), "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": workload_name(args.level, args.gpus)},
+            "config": {"workload": workload_name(args.level, args.gpus, args.mesh)},
             "cpu_baseline": base, "e2e": {"value": v, "unit": "GDoF/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
 
@@ -219,15 +238,16 @@ def main():
         k, val = kv.split("=")
         lib.dll.hb_set_tuning(k.encode(), int(val))
     from hyteg_b200 import comm
+    # weak scaling (BASELINE configs[4]): the spherical shell with one radial layer of 60 macro-tets per GPU, partitioned into connected
+    # blocks by the greedy balancer (every rank has several neighbour ranks); the ghost layers travel over NVLink inside the step:
+    # remote stores into the neighbours' peer-memory windows (HB_P2P=0: pack -> ncclSend/ncclRecv -> unpack)
+    (v, c), mesh_kind = workload_mesh(world, args.mesh)
+    cell_rank = None
     if world > 1:
-        # weak scaling: a box of `world` unit cubes (6 macro-tets each), macro-cells partitioned in contiguous blocks so that
-        # every rank owns one cube; the ghost layers on the faces between the cubes travel over NVLink inside the step: remote
-        # stores into the neighbours' peer-memory windows (HB_P2P=0: pack -> ncclSend/ncclRecv -> unpack)
-        v, c = meshes.cuboid(world, 1, 1, hi=(float(world), 1.0, 1.0))
         comm.init_nccl(lib)
-    else:
-        v, c = meshes.cube_6el()
-    st = api.PrimitiveStorage(v, c, rank, world)
+        if mesh_kind == "shell":
+            cell_rank = meshes.partition_greedy(c, world)
+    st = api.PrimitiveStorage(v, c, rank, world, cell_rank=cell_rank)
     st.setMeshBoundaryFlagsOnBoundary(1, 0, True)
     A = api.P1ConstantLaplaceOperator(st, 0, L)
     src, dst, rhs = (api.P1Function(n, st, 0, L) for n in ("src", "dst", "rhs"))
@@ -359,7 +379,7 @@ def main():
     parity_ok = None
     if world > 1:
         Lc = 4
-        st1 = api.PrimitiveStorage(v, c, 0, 1)
+        st1 = api.PrimitiveStorage(v, c, 0, 1)  # the whole macro mesh on this GPU
         st1.setMeshBoundaryFlagsOnBoundary(1, 0, True)
         ok = True
         A1, Ap = api.P1ConstantLaplaceOperator(st1, 0, Lc), api.P1ConstantLaplaceOperator(st, 0, Lc)
@@ -407,19 +427,24 @@ def main():
               "setup_s": setup_s}
         del Ap2, ps, pd, pk, sts
 
+    npeers, nsend, nrecv = st.exchange_info(L)
+    npeers_max = npeers
+    if world > 1:
+        t = torch.tensor([float(npeers), float(nsend)], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        npeers_max, nsend = int(t[0].item()), int(t[1].item())
     if rank == 0:
         peak, which = measured_peak()
         gd = lambda ms: ndof / (ms * 1e-3) / 1e9
         ndof_rank = ndof / world
         achieved = BYTES_PER_DOF["apply"] * n_interior / (ms_interior * 1e-3) / 1e9
         whole = BYTES_PER_DOF["apply"] * ndof_rank / (ms_apply * 1e-3) / 1e9
-        npeers, nsend, nrecv = st.exchange_info(L)
         xmode = "NVLink peer-memory windows, one kernel per exchange" if (world > 1 and comm.p2p_active(lib)[0]) else "NCCL send/recv"
         line = {"metric": "P1 constant-stencil apply throughput", "value": gd(ms_apply), "unit": "GDoF/s", "n_gpus": world,
                 "steps": args.steps, "warmup": W, "ms_per_step": ms_apply, "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-                "config": {"workload": workload_name(L, world), "dofs_per_gpu": int(ndof_rank),
-                           "exchange": None if world == 1 else f"ghost exchange of {8 * nsend} B with {npeers} neighbour rank(s) (rank 0) inside every step ({xmode})",
+                "config": {"workload": workload_name(L, world, args.mesh), "dofs_per_gpu": int(ndof_rank), "dofs_total": int(ndof),
+                           "exchange": None if world == 1 else f"ghost exchange of up to {8 * nsend} B per rank with up to {npeers_max} neighbour ranks inside every step ({xmode})",
                            "l2": "src+dst arrays %.0f MB > 126 MB L2" % (2 * 8 * n_arr / 1e6),
                            "multi_gpu": f"macro-cells partitioned, ghost layers over {xmode}" if world > 1 else "single"},
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
@@ -441,7 +466,7 @@ def main():
                         "note": "%d requests in flight on %d streams (uploads overlap downloads, PCIe full duplex)" % (n_lanes, n_lanes)},
                 "gpu_launches": 2 * args.steps + (2 * args.steps if world > 1 else 0), "clocks": clk.summary()}
         if not args.no_cpu_baseline and world == 1:
-            line["cpu_baseline"] = cpu_reference_apply(min(L, 8), budget_s=10.0)
+            line["cpu_baseline"] = cpu_reference_apply(min(L, 8), budget_s=10.0, mesh=args.mesh)
             if line["cpu_baseline"]:
                 line["cpu_baseline"].pop("steps", None)
         print(json.dumps(line))

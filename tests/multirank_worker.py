@@ -33,12 +33,15 @@ def main():
         mesh = meshes.cuboid(2, 1, 1)
     elif mesh_name == "shell":  # BASELINE config[4] family: icosahedral spherical shell (60 macro-cells), many neighbours per rank
         mesh = meshes.spherical_shell(2, 2)
+    elif mesh_name == "shell_greedy":  # two radial layers, connected blocks from the greedy balancer: every rank has several neighbours
+        mesh = meshes.spherical_shell(2, 3)
     else:
         mesh = meshes.golden(mesh_name)
+    cell_rank = meshes.partition_greedy(mesh[1], world) if mesh_name == "shell_greedy" else None
     L = 3
 
     # ---- apply / Jacobi / BLAS-1 / transfer against the oracle ---------------------------------------------------
-    s = pc.Setup(lib, mesh, L - 1, L, rank, world)
+    s = pc.Setup(lib, mesh, L - 1, L, rank, world, cell_rank)
     assert 0 < s.st.num_local_cells < len(mesh[1])
     npeers, nsend, nrecv = s.st.exchange_info(L)
     assert 1 <= npeers <= world - 1 and nsend > 0 and nrecv > 0, (npeers, nsend, nrecv)
@@ -80,7 +83,7 @@ def main():
 
     # ---- SOR sweeps and V-cycles: identical to the one-rank run ----------------------------------------------------
     def run(r, w):
-        t = pc.Setup(lib, mesh, 0, L, r, w)
+        t = pc.Setup(lib, mesh, 0, L, r, w, cell_rank)
         fx, fb, fr = t.fn("x"), t.fn("b"), t.fn("r")
         t.put(fx, x, L)
         t.put(fb, b, L)

@@ -15,9 +15,9 @@ def rel(a, b):
 
 
 class Setup:
-    def __init__(self, lib, mesh, min_level, max_level, rank=0, n_ranks=1):
+    def __init__(self, lib, mesh, min_level, max_level, rank=0, n_ranks=1, cell_rank=None):
         v, c = mesh
-        self.st = api.PrimitiveStorage(v, c, rank, n_ranks, lib=lib)
+        self.st = api.PrimitiveStorage(v, c, rank, n_ranks, lib=lib, cell_rank=cell_rank if n_ranks > 1 else None)
         self.st.setMeshBoundaryFlagsOnBoundary(1, 0, True)
         self.o = po.P1Oracle(v, c, min_level, max_level)
         self.A = api.P1ConstantLaplaceOperator(self.st, min_level, max_level)

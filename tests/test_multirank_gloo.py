@@ -16,7 +16,7 @@ def free_port():
         return s.getsockname()[1]
 
 
-@pytest.mark.parametrize("mesh,world", [("cube_6el", 2), ("cube_24el", 2), ("regular_octahedron_8el", 3), ("shell", 4)])
+@pytest.mark.parametrize("mesh,world", [("cube_6el", 2), ("cube_24el", 2), ("regular_octahedron_8el", 3), ("shell", 4), ("shell_greedy", 4)])
 def test_partitioned_matches_one_rank(emul_lib, mesh, world):
     port = free_port()
     procs = []
