@@ -435,3 +435,63 @@ class P2toP2QuadraticProlongation:
 
     def prolongateAndAdd(self, f, source_level, flag):
         f.lib.check(f.lib.dll.hb_p2_prolongate_and_add(f.h, source_level, flag))
+
+
+class P2ToP1ElementwiseBlendingDivOperator(P2ElementwiseOperator):
+    """P2ToP1ElementwiseBlendingDiv{x,y,z}Operator (elementwiseoperators/P2ToP1ElementwiseOperator.hpp:264-266)"""
+
+    def __init__(self, storage, min_level, max_level, component):
+        super().__init__(storage, min_level, max_level, storage.lib.dll.hb_p2_div_create(storage.h, min_level, max_level, component), None)
+
+    def apply(self, src, dst, level, flag, update=Replace):
+        self.lib.check(self.lib.dll.hb_p2operator_apply_p2_to_p1(self.h, src.h, dst.h, level, flag, update))
+
+
+class P1ToP2ElementwiseBlendingDivTOperator(P2ElementwiseOperator):
+    """P1ToP2ElementwiseBlendingDivT{x,y,z}Operator (elementwiseoperators/P1ToP2ElementwiseOperator.hpp:275-277)"""
+
+    def __init__(self, storage, min_level, max_level, component):
+        super().__init__(storage, min_level, max_level, storage.lib.dll.hb_p2_divt_create(storage.h, min_level, max_level, component), None)
+
+    def apply(self, src, dst, level, flag, update=Replace):
+        self.lib.check(self.lib.dll.hb_p2operator_apply_p1_to_p2(self.h, src.h, dst.h, level, flag, update))
+
+
+class P2ElementwiseBlendingEpsilonOperator(P2ElementwiseOperator):
+    """P2ElementwiseBlendingEpsilonOperator (elementwiseoperators/P2ElementwiseEpsilonOperator.hpp:112-170) on a P2 vector function
+    (a list of three P2Functions), all nine blocks in one fused kernel; mu: P2Function, callable or None"""
+
+    def __init__(self, storage, min_level, max_level, mu=None):
+        kh = mu.h if isinstance(mu, P2Function) else None
+        super().__init__(storage, min_level, max_level, storage.lib.dll.hb_p2_epsilon_vector_create(storage.h, min_level, max_level, kh), mu)
+
+    def apply(self, src, dst, level, flag, update=Replace):
+        hs = (C.c_void_p * 3)(*[f.h for f in src])
+        hd = (C.c_void_p * 3)(*[f.h for f in dst])
+        self.lib.check(self.lib.dll.hb_p2operator_apply_vector(self.h, hs, hd, level, flag, update))
+
+
+class P2P1TaylorHoodFunction:
+    """P2P1TaylorHoodFunction (composites/P2P1TaylorHoodFunction.hpp): uvw = three P2Functions, p = a P1Function"""
+
+    def __init__(self, name, storage, min_level, max_level):
+        self.uvw = [P2Function("%s_%s" % (name, c), storage, min_level, max_level) for c in "uvw"]
+        self.p = P1Function(name + "_p", storage, min_level, max_level)
+
+
+class P2P1ElementwiseBlendingEpsilonStokesOperator:
+    """The Taylor-Hood Stokes operator with the epsilon (full viscous) velocity block: A u + B^T p ; B u -- the composite of
+    P2P1ElementwiseBlendingStokesOperator::apply (elementwiseoperators/P2P1ElementwiseBlendingStokesOperator.hpp:91-100) with
+    P2ElementwiseBlendingEpsilonOperator as A (BASELINE config 4; src/hyteg_operators_composites/stokes/P2P1StokesEpsilonOperator.hpp)"""
+
+    def __init__(self, storage, min_level, max_level, mu=None):
+        self.A = P2ElementwiseBlendingEpsilonOperator(storage, min_level, max_level, mu)
+        self.div = [P2ToP1ElementwiseBlendingDivOperator(storage, min_level, max_level, c) for c in range(3)]
+        self.divT = [P1ToP2ElementwiseBlendingDivTOperator(storage, min_level, max_level, c) for c in range(3)]
+
+    def apply(self, src, dst, level, flag, update=Replace):
+        assert update == Replace
+        self.A.apply(src.uvw, dst.uvw, level, flag, Replace)
+        for c in range(3):
+            self.divT[c].apply(src.p, dst.uvw[c], level, flag, Add)
+            self.div[c].apply(src.uvw[c], dst.p, level, flag, Replace if c == 0 else Add)

@@ -113,6 +113,12 @@ _SIGNATURES = {
     "hb_p2operator_quadrature_points": (C.c_int, [_vp, C.c_int, _dp]),
     "hb_p2operator_set_sampled_coefficient": (C.c_int, [_vp, C.c_int, _dp]),
     "hb_p2operator_apply": (C.c_int, [_vp, _vp, _vp, C.c_int, C.c_int, C.c_int]),
+    "hb_p2_div_create": (_vp, [_vp, C.c_int, C.c_int, C.c_int]),
+    "hb_p2_divt_create": (_vp, [_vp, C.c_int, C.c_int, C.c_int]),
+    "hb_p2_epsilon_vector_create": (_vp, [_vp, C.c_int, C.c_int, _vp]),
+    "hb_p2operator_apply_p2_to_p1": (C.c_int, [_vp, _vp, _vp, C.c_int, C.c_int, C.c_int]),
+    "hb_p2operator_apply_p1_to_p2": (C.c_int, [_vp, _vp, _vp, C.c_int, C.c_int, C.c_int]),
+    "hb_p2operator_apply_vector": (C.c_int, [_vp, C.POINTER(_vp), C.POINTER(_vp), C.c_int, C.c_int, C.c_int]),
     "hb_p2_restrict": (C.c_int, [_vp, C.c_int, C.c_int]),
     "hb_p2_prolongate": (C.c_int, [_vp, C.c_int, C.c_int]),
     "hb_p2_prolongate_and_add": (C.c_int, [_vp, C.c_int, C.c_int]),

@@ -83,7 +83,7 @@ HB_CONSTANT double hb_p2_q2[4][5] = { { HB_QA, HB_QA, HB_QA, HB_QB, 0.0416666666
 
 int hb_p2_num_quad_points( int form )
 {
-   return form == HB_P2_EPSILON ? 4 : 11;
+   return hb_p2_form_q2( form ) ? 4 : 11;
 }
 
 // ---- geometry ----------------------------------------------------------------------------------------------------------------
@@ -134,7 +134,10 @@ __host__ __device__ __forceinline__ void hb_p2_vertex_pos( const HbP2CellGeom& g
 }
 
 // ---- the element kernel --------------------------------------------------------------------------------------------------------
+// NC = 1: scalar forms (div-k-grad, one epsilon block, div, divT); NC = 3: the whole epsilon operator on a vector function (the
+// geometry of a quadrature point is evaluated once for all nine blocks).
 
+template < int NC >
 __global__ void hb_p2_elem_kernel( const HbP2View pv, const HbP2ElemArgs a )
 {
    const int perCell = ( pv.nAnchors + blockDim.x - 1 ) / blockDim.x;
@@ -148,27 +151,33 @@ __global__ void hb_p2_elem_kernel( const HbP2View pv, const HbP2ElemArgs a )
    const HbP2CellGeom g = pv.geom[cell];
    const size_t       vb = (size_t) cell * pv.vCellSize, eb = (size_t) cell * pv.eCellSize;
    const double       invN = 1.0 / N;
-   const int          nq = a.form == HB_P2_EPSILON ? 4 : 11;
+   const bool         q2   = hb_p2_form_q2( a.form );
+   const int          nq   = q2 ? 4 : 11;
+   const bool         p1In = a.form == HB_P2_DIVT, p1Out = a.form == HB_P2_DIV;
    for ( int t = 0; t < 6; t++ )
    {
       if ( x + y + z > N - hb_p2_slack[t] )
          continue;
       // local DoFs
       int    vi[4], ei[6];
-      double X[4][3], u[10], kk[10];
+      double X[4][3], u[NC][10], kk[10];
 #pragma unroll
       for ( int k = 0; k < 4; k++ )
       {
          const int vx = x + hb_p2_vert[t][k][0], vy = y + hb_p2_vert[t][k][1], vz = z + hb_p2_vert[t][k][2];
          vi[k]        = hb_index( N, vx, vy, vz );
          hb_p2_vertex_pos( g, invN, vx, vy, vz, X[k] );
-         u[k] = a.srcV[vb + vi[k]];
+#pragma unroll
+         for ( int c = 0; c < NC; c++ )
+            u[c][k] = a.srcV[c][vb + vi[k]];
       }
 #pragma unroll
       for ( int k = 0; k < 6; k++ )
       {
-         ei[k]    = hb_edge_index( N, hb_p2_edge[t][k][0], x + hb_p2_edge[t][k][1], y + hb_p2_edge[t][k][2], z + hb_p2_edge[t][k][3] );
-         u[4 + k] = a.srcE[eb + ei[k]];
+         ei[k] = hb_edge_index( N, hb_p2_edge[t][k][0], x + hb_p2_edge[t][k][1], y + hb_p2_edge[t][k][2], z + hb_p2_edge[t][k][3] );
+#pragma unroll
+         for ( int c = 0; c < NC; c++ )
+            u[c][4 + k] = p1In ? 0.0 : a.srcE[c][eb + ei[k]];
       }
       if ( a.kV )
       {
@@ -188,14 +197,16 @@ __global__ void hb_p2_elem_kernel( const HbP2View pv, const HbP2ElemArgs a )
          J[3 * d + 1] = X[2][d] - X[0][d];
          J[3 * d + 2] = X[3][d] - X[0][d];
       }
-      double yv[10];
+      double yv[NC][10];
 #pragma unroll
-      for ( int k = 0; k < 10; k++ )
-         yv[k] = 0.0;
+      for ( int c = 0; c < NC; c++ )
+#pragma unroll
+         for ( int k = 0; k < 10; k++ )
+            yv[c][k] = 0.0;
       const double* kq = a.kq ? a.kq + ( ( (size_t) cell * 6 + t ) * pv.nAnchors + ai ) * nq : nullptr;
       for ( int q = 0; q < nq; q++ )
       {
-         const double* Q = a.form == HB_P2_EPSILON ? hb_p2_q2[q] : hb_p2_q4[q];
+         const double* Q = q2 ? hb_p2_q2[q] : hb_p2_q4[q];
          const double  lam[4] = { Q[0], Q[1], Q[2], Q[3] };
          double        M[9], Mi[9];
          if ( pv.blending )
@@ -233,59 +244,103 @@ __global__ void hb_p2_elem_kernel( const HbP2View pv, const HbP2ElemArgs a )
                kval += kk[4 + k] * ( 4.0 * lam[hb_p2_pair[k][0]] * lam[hb_p2_pair[k][1]] );
          }
          const double s = Q[4] * kval * fabs( det );
-         // reference gradient of u in barycentric directions: c[k] = coefficient of grad lambda_k
-         double c[4];
+         // physical gradient of every component: grad u = M^-T gradhat u, gradhat u from the coefficients c[k] of grad lambda_k
+         double gu[NC][3];
+         double pval = 0.0; // HB_P2_DIVT: the P1 source at the quadrature point
 #pragma unroll
-         for ( int k = 0; k < 4; k++ )
-            c[k] = u[k] * ( 4.0 * lam[k] - 1.0 );
-#pragma unroll
-         for ( int k = 0; k < 6; k++ )
+         for ( int cc = 0; cc < NC; cc++ )
          {
-            const int pa = hb_p2_pair[k][0], pb = hb_p2_pair[k][1];
-            c[pa] += 4.0 * u[4 + k] * lam[pb];
-            c[pb] += 4.0 * u[4 + k] * lam[pa];
-         }
-         const double th[3] = { c[1] - c[0], c[2] - c[0], c[3] - c[0] }; // gradhat u (grad lambda_0 = -(1,1,1), grad lambda_k = e_k)
-         // grad u = M^-T gradhat u
-         double gu[3];
+            double c[4];
+            if ( p1In )
+            {
 #pragma unroll
-         for ( int d = 0; d < 3; d++ )
-            gu[d] = Mi[d] * th[0] + Mi[3 + d] * th[1] + Mi[6 + d] * th[2];
-         double f[3];
-         if ( a.form == HB_P2_EPSILON )
-         {
+               for ( int k = 0; k < 4; k++ )
+                  pval += u[cc][k] * lam[k];
+               gu[cc][0] = gu[cc][1] = gu[cc][2] = 0.0;
+               continue;
+            }
+#pragma unroll
+            for ( int k = 0; k < 4; k++ )
+               c[k] = u[cc][k] * ( 4.0 * lam[k] - 1.0 );
+#pragma unroll
+            for ( int k = 0; k < 6; k++ )
+            {
+               const int pa = hb_p2_pair[k][0], pb = hb_p2_pair[k][1];
+               c[pa] += 4.0 * u[cc][4 + k] * lam[pb];
+               c[pb] += 4.0 * u[cc][4 + k] * lam[pa];
+            }
+            const double th[3] = { c[1] - c[0], c[2] - c[0], c[3] - c[0] }; // grad lambda_0 = -(1,1,1), grad lambda_k = e_k
 #pragma unroll
             for ( int d = 0; d < 3; d++ )
-               f[d] = ( a.compC == a.compD ? s * gu[d] : 0.0 ) + ( d == a.compD ? s * gu[a.compC] : 0.0 );
+               gu[cc][d] = Mi[d] * th[0] + Mi[3 + d] * th[1] + Mi[6 + d] * th[2];
          }
-         else
+         if ( p1Out )
          {
+            // y_i (P1) -= s lambda_i d_c u
+            const double v = -s * gu[0][a.compC];
+#pragma unroll
+            for ( int k = 0; k < 4; k++ )
+               yv[0][k] += lam[k] * v;
+            continue;
+         }
+#pragma unroll
+         for ( int cc = 0; cc < NC; cc++ )
+         {
+            double f[3];
+            if ( NC == 3 ) // row cc of mu ( grad u + grad u^T )
+            {
+#pragma unroll
+               for ( int d = 0; d < 3; d++ )
+                  f[d] = s * ( gu[cc][d] + gu[d < NC ? d : 0][cc] );
+            }
+            else if ( a.form == HB_P2_EPSILON )
+            {
+#pragma unroll
+               for ( int d = 0; d < 3; d++ )
+                  f[d] = ( a.compC == a.compD ? s * gu[0][d] : 0.0 ) + ( d == a.compD ? s * gu[0][a.compC] : 0.0 );
+            }
+            else if ( p1In )
+            {
+#pragma unroll
+               for ( int d = 0; d < 3; d++ )
+                  f[d] = d == a.compC ? -s * pval : 0.0;
+            }
+            else
+            {
+#pragma unroll
+               for ( int d = 0; d < 3; d++ )
+                  f[d] = s * gu[0][d];
+            }
+            // hh = M^-1 f ; y_i += gradhat phi_i . hh
+            double hh[3];
 #pragma unroll
             for ( int d = 0; d < 3; d++ )
-               f[d] = s * gu[d];
-         }
-         // hh = M^-1 f ; y_i += gradhat phi_i . hh
-         double hh[3];
+               hh[d] = Mi[3 * d] * f[0] + Mi[3 * d + 1] * f[1] + Mi[3 * d + 2] * f[2];
+            const double h[4] = { -( hh[0] + hh[1] + hh[2] ), hh[0], hh[1], hh[2] };
 #pragma unroll
-         for ( int d = 0; d < 3; d++ )
-            hh[d] = Mi[3 * d] * f[0] + Mi[3 * d + 1] * f[1] + Mi[3 * d + 2] * f[2];
-         const double h[4] = { -( hh[0] + hh[1] + hh[2] ), hh[0], hh[1], hh[2] };
+            for ( int k = 0; k < 4; k++ )
+               yv[cc][k] += ( 4.0 * lam[k] - 1.0 ) * h[k];
 #pragma unroll
-         for ( int k = 0; k < 4; k++ )
-            yv[k] += ( 4.0 * lam[k] - 1.0 ) * h[k];
-#pragma unroll
-         for ( int k = 0; k < 6; k++ )
-         {
-            const int pa = hb_p2_pair[k][0], pb = hb_p2_pair[k][1];
-            yv[4 + k] += 4.0 * ( lam[pa] * h[pb] + lam[pb] * h[pa] );
+            for ( int k = 0; k < 6; k++ )
+            {
+               const int pa = hb_p2_pair[k][0], pb = hb_p2_pair[k][1];
+               yv[cc][4 + k] += 4.0 * ( lam[pa] * h[pb] + lam[pb] * h[pa] );
+            }
          }
       }
 #pragma unroll
-      for ( int k = 0; k < 4; k++ )
-         hb_atomic_add( a.accV + vb + vi[k], yv[k] );
+      for ( int c = 0; c < NC; c++ )
+      {
 #pragma unroll
-      for ( int k = 0; k < 6; k++ )
-         hb_atomic_add( a.accE + eb + ei[k], yv[4 + k] );
+         for ( int k = 0; k < 4; k++ )
+            hb_atomic_add( a.accV[c] + vb + vi[k], yv[c][k] );
+         if ( !p1Out )
+         {
+#pragma unroll
+            for ( int k = 0; k < 6; k++ )
+               hb_atomic_add( a.accE[c] + eb + ei[k], yv[c][4 + k] );
+         }
+      }
    }
 }
 
@@ -293,8 +348,12 @@ void hb_p2_launch_elements( const HbP2View& pv, const HbP2ElemArgs& a, cudaStrea
 {
    const int block   = 128;
    const int perCell = ( pv.nAnchors + block - 1 ) / block;
-   if ( pv.nCells * perCell > 0 )
-      HB_LAUNCH( hb_p2_elem_kernel, pv.nCells * perCell, block, st, pv, a );
+   if ( pv.nCells * perCell <= 0 )
+      return;
+   if ( a.form == HB_P2_EPSILON_VECTOR )
+      HB_LAUNCH( hb_p2_elem_kernel< 3 >, pv.nCells * perCell, block, st, pv, a );
+   else
+      HB_LAUNCH( hb_p2_elem_kernel< 1 >, pv.nCells * perCell, block, st, pv, a );
 }
 
 // ---- finalize: interior entries, then the interface groups ------------------------------------------------------------------------
@@ -317,7 +376,8 @@ __global__ void hb_p2_finalize_interior_kernel( const HbP2View pv, const HbP2Fin
       return;
    double*       d   = edge ? a.dstE : a.dstV;
    const double* acc = edge ? a.accE : a.accV;
-   d[j]              = ( a.beta == 0.0 ? 0.0 : a.beta * d[j] ) + acc[j];
+   if ( d )
+      d[j] = ( a.beta == 0.0 ? 0.0 : a.beta * d[j] ) + acc[j];
 }
 
 __global__ void hb_p2_finalize_groups_kernel( const HbP2View pv, const HbP2FinalizeArgs a )
@@ -329,6 +389,8 @@ __global__ void hb_p2_finalize_groups_kernel( const HbP2View pv, const HbP2Final
       return;
    const long long EDGE = 1ll << 62;
    const long long e0 = a.grpStart[gidx], e1 = a.grpStart[gidx + 1];
+   if ( ( a.grpEntry[e0] & EDGE ) ? a.dstE == nullptr : a.dstV == nullptr )
+      return;
    double          sum = 0.0;
    for ( long long e = e0; e < e1; e++ ) // ascending macro-cell id: every run adds in the same order
    {
@@ -423,7 +485,7 @@ __global__ void hb_p2_quad_points_kernel( const HbP2View pv, const int form, dou
    const int          N  = pv.N;
    const HbBndPoint   p  = pv.anchors[ai];
    const HbP2CellGeom g  = pv.geom[cell];
-   const int          nq = form == HB_P2_EPSILON ? 4 : 11;
+   const int          nq = hb_p2_form_q2( form ) ? 4 : 11;
    for ( int t = 0; t < 6; t++ )
    {
       double* o = out + ( ( (size_t) cell * 6 + t ) * pv.nAnchors + ai ) * nq * 3;
@@ -438,7 +500,7 @@ __global__ void hb_p2_quad_points_kernel( const HbP2View pv, const int form, dou
          hb_p2_vertex_pos( g, 1.0 / N, p.x + hb_p2_vert[t][k][0], p.y + hb_p2_vert[t][k][1], p.z + hb_p2_vert[t][k][2], X[k] );
       for ( int q = 0; q < nq; q++ )
       {
-         const double* Q = form == HB_P2_EPSILON ? hb_p2_q2[q] : hb_p2_q4[q];
+         const double* Q = hb_p2_form_q2( form ) ? hb_p2_q2[q] : hb_p2_q4[q];
          double        xq[3], F[3], DF[9];
          for ( int d = 0; d < 3; d++ )
             xq[d] = Q[0] * X[0][d] + Q[1] * X[1][d] + Q[2] * X[2][d] + Q[3] * X[3][d];

@@ -13,8 +13,15 @@
 enum HbP2Form
 {
    HB_P2_DIVKGRAD = 0, // int k grad(u) . grad(v), 11-point degree-4 rule (forms/form_hyteg_generated/p2/p2_div_k_grad_blending_q4.cpp)
-   HB_P2_EPSILON  = 1  // int 2 mu eps(phi_j e_d) : eps(phi_i e_c), 4-point degree-2 rule (p2_epsilonvar_blending_q2.cpp)
+   HB_P2_EPSILON  = 1, // int 2 mu eps(phi_j e_d) : eps(phi_i e_c), 4-point degree-2 rule (p2_epsilonvar_blending_q2.cpp)
+   HB_P2_DIV      = 2, // P2 -> P1:  - int psi_i d_c phi_j           (p2_to_p1/p2_to_p1_div_blending_q2.cpp, same 4-point rule)
+   HB_P2_DIVT     = 3, // P1 -> P2:  - int d_c phi_i psi_j           (p1_to_p2/p1_to_p2_divt_blending_q2.cpp)
+   HB_P2_EPSILON_VECTOR = 4 // all nine epsilon blocks at once on a P2 vector function: y^c_i = int mu ( grad u + grad u^T )_c . grad phi_i
 };
+__host__ __device__ __forceinline__ bool hb_p2_form_q2( int form )
+{
+   return form != HB_P2_DIVKGRAD;
+}
 
 __host__ __device__ __forceinline__ int hb_p2_tet( int w )
 {
@@ -63,10 +70,10 @@ struct HbP2View
 
 struct HbP2ElemArgs
 {
-   const double* srcV;
-   const double* srcE;
-   double*       accV; // zeroed accumulators, same layout as the function
-   double*       accE;
+   const double* srcV[3]; // components 1, 2 only for HB_P2_EPSILON_VECTOR; srcE null for HB_P2_DIVT (P1 source)
+   const double* srcE[3];
+   double*       accV[3]; // zeroed accumulators, same layout as the function; accE null for HB_P2_DIV (P1 destination)
+   double*       accE[3];
    const double* kV;   // coefficient as a P2 function (or null)
    const double* kE;
    const double* kq;   // coefficient sampled at the quadrature points [cell][type][anchor][q] (or null; null and no kV: k = 1)
@@ -76,7 +83,7 @@ struct HbP2ElemArgs
 
 struct HbP2FinalizeArgs
 {
-   double*       dstV;
+   double*       dstV; // either part may be null: it is left alone then
    double*       dstE;
    const double* accV;
    const double* accE;

@@ -243,6 +243,18 @@ int            hb_p2operator_set_sampled_coefficient( hb_p2operator* op, int lev
 /* Operator::apply( src, dst, level, flag, updateType ) -- P2ElementwiseOperator::gemv (P2ElementwiseOperator.cpp:109-330) */
 int hb_p2operator_apply( hb_p2operator* op, const hb_p2function* src, hb_p2function* dst, int level, int flag, int update_type );
 
+/* P2ToP1ElementwiseBlendingDiv{x,y,z}Operator (P2ToP1ElementwiseOperator.hpp:264-266, forms::p2_to_p1_div_c_blending_q2) and
+ * P1ToP2ElementwiseBlendingDivT{x,y,z}Operator (P1ToP2ElementwiseOperator.hpp:275-277, forms::p1_to_p2_divt_c_blending_q2): the B and
+ * B^T blocks of P2P1ElementwiseBlendingStokesOperator (P2P1ElementwiseBlendingStokesOperator.hpp:91-100); component 0..2 */
+hb_p2operator* hb_p2_div_create( hb_storage* st, int min_level, int max_level, int component );
+hb_p2operator* hb_p2_divt_create( hb_storage* st, int min_level, int max_level, int component );
+int hb_p2operator_apply_p2_to_p1( hb_p2operator* op, const hb_p2function* src, hb_function* dst, int level, int flag, int update_type );
+int hb_p2operator_apply_p1_to_p2( hb_p2operator* op, const hb_function* src, hb_p2function* dst, int level, int flag, int update_type );
+/* P2ElementwiseBlendingEpsilonOperator (P2ElementwiseEpsilonOperator.hpp:112-170) as ONE fused kernel: all nine blocks on a P2 vector
+ * function (three P2Functions), the geometry of a quadrature point evaluated once */
+hb_p2operator* hb_p2_epsilon_vector_create( hb_storage* st, int min_level, int max_level, const hb_p2function* mu );
+int hb_p2operator_apply_vector( hb_p2operator* op, hb_p2function* const* src3, hb_p2function* const* dst3, int level, int flag, int update_type );
+
 /* P2toP2QuadraticRestriction::restrict / P2toP2QuadraticProlongation::prolongate / prolongateAndAdd
  * (src/hyteg/gridtransferoperators/P2toP2QuadraticRestriction.cpp:131-251, P2toP2QuadraticProlongation.cpp) */
 int hb_p2_restrict( hb_p2function* f, int source_level, int flag );

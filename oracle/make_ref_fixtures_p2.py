@@ -38,6 +38,18 @@ def main():
             for i, j in ((0, 0), (0, 1), (1, 2), (2, 0), (2, 2)):
                 out["shell_L2_epsilon_%d%d_inner" % (i, j)] = rb.p2_apply(s, o, x, L, form="epsilon", dst=d0, flag=1, update=0, shell=1, i=i, j=j)
         print("shell level", L, "done", flush=True)
+    # B and B^T blocks of the Stokes operator on the shell (P2ToP1ElementwiseBlendingDiv*, P1ToP2ElementwiseBlendingDivT*), level 2
+    o = p2.P2Oracle(v, c, 2, shell=True)
+    x, d0 = p2_inputs(o.n, 302)
+    phys = o.dof_physical_coordinates()
+    tol = 0.05 * rb.min_spacing(v, c, 2)
+    for comp in (0, 1, 2):
+        oute = os.path.join(s.dir, "oe.bin")
+        _, cl = s.run("p2top1", 2, src=s.cloud(phys, x), oute=oute, comp=comp, flag=1, shell=1)
+        out["shell_L2_div_%d_inner" % comp] = rb.to_global(o.xyz[: o.nv], cl, tol)
+        _, cl = s.run("p2fromp1", 2, src=s.cloud(phys[: o.nv], d0[: o.nv]), oute=oute, comp=comp, flag=1, shell=1)
+        de = np.fromfile(oute).reshape(-1, 4)
+        out["shell_L2_divt_%d_inner" % comp] = np.concatenate([rb.to_global(o.xyz[: o.nv], cl, tol), rb.to_global(o.xyz[o.nv:], (de[:, :3], de[:, 3]), tol)])
     # IcosahedralShellMap samples per macro-cell (cells identified by their centroid)
     for nt, nr in ((3, 2), (2, 3)):
         vv, cc = meshes.spherical_shell(nt, nr, 0.5, 1.0)

@@ -306,6 +306,30 @@ class P2Oracle:
                 A += (s[:, None, None] if np.ndim(s) else s) * np.einsum("eik,ejk->eij", G, G)
         return A
 
+    def div_element_matrices(self, comp):
+        """[ne,4,10]: P2 -> P1, b_ij = - int psi_i d_comp phi_j  (forms/form_hyteg_generated/p2_to_p1/p2_to_p1_div_blending_q2.cpp);
+        the transpose [ne,10,4] is p1_to_p2_divt_blending_q2 (P1 -> P2)"""
+        X = self.el_X
+        J = np.stack([X[:, 1] - X[:, 0], X[:, 2] - X[:, 0], X[:, 3] - X[:, 0]], axis=2)
+        B = np.zeros((len(X), 4, 10))
+        P = self.params[self.el_cell] if self.shell else None
+        for lam, w in zip(VR1_POINTS, VR1_WEIGHTS):
+            _, gref = p2_shape(lam)
+            xq = np.einsum("k,eki->ei", lam, X)
+            M = shell_eval_df(P, xq) @ J if self.shell else J
+            G = gref[None, :, :] @ np.linalg.inv(M)
+            B -= (w * np.abs(np.linalg.det(M)))[:, None, None] * lam[None, :, None] * G[:, None, :, comp]
+        return B
+
+    def div_matrix(self, comp):
+        """P2ToP1ElementwiseBlendingDiv{x,y,z}Operator as a matrix [nv, n]"""
+        B = self.div_element_matrices(comp)
+        rows = np.repeat(self.el_dofs[:, :4], 10, axis=1).ravel()
+        cols = np.tile(self.el_dofs, (1, 4)).ravel()
+        M = sp.csr_matrix((B.ravel(), (rows, cols)), shape=(self.nv, self.n))
+        M.sum_duplicates()
+        return M
+
     def matrix(self, **kw):
         A = self.element_matrices(**kw)
         rows = np.repeat(self.el_dofs, 10, axis=1).ravel()

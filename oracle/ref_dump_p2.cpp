@@ -14,7 +14,9 @@
 
 #include "hyteg/edgedofspace/EdgeDoFIndexing.hpp"
 #include "hyteg/edgedofspace/EdgeDoFMacroCell.hpp"
+#include "hyteg/elementwiseoperators/P1ToP2ElementwiseOperator.hpp"
 #include "hyteg/elementwiseoperators/P2ElementwiseOperator.hpp"
+#include "hyteg/elementwiseoperators/P2ToP1ElementwiseOperator.hpp"
 #include "hyteg/forms/form_hyteg_generated/p2/p2_div_k_grad_blending_q4.hpp"
 #include "hyteg/forms/form_hyteg_generated/p2/p2_epsilonvar_blending_q2.hpp"
 #include "hyteg/geometry/IcosahedralShellMap.hpp"
@@ -138,6 +140,39 @@ int mainP2( const Args& a )
          std::fprintf( stderr, "unknown form %s\n", form.c_str() );
          return 1;
       }
+   }
+   else if ( a.cmd == "p2top1" || a.cmd == "p2fromp1" )
+   {
+      // B and B^T blocks of the Stokes operator: P2ToP1ElementwiseBlendingDiv{x,y,z}Operator / P1ToP2ElementwiseBlendingDivT{x,y,z}Operator
+      const int            comp = int( a.num( "comp", 0 ) );
+      const DoFType        flag = DoFType( int( a.num( "flag", 1 ) ) );
+      P2Function< real_t > u( "u", st, L, L );
+      P1Function< real_t > q( "q", st, L, L );
+      if ( a.cmd == "p2top1" )
+      {
+         setP2FromCloud( u, a.str( "src" ), h, L );
+         if ( comp == 0 )
+            P2ToP1ElementwiseBlendingDivxOperator( st, L, L ).apply( u, q, L, flag, Replace );
+         else if ( comp == 1 )
+            P2ToP1ElementwiseBlendingDivyOperator( st, L, L ).apply( u, q, L, flag, Replace );
+         else
+            P2ToP1ElementwiseBlendingDivzOperator( st, L, L ).apply( u, q, L, flag, Replace );
+         u.getVertexDoFFunction().assign( { 1.0 }, { q }, L, All );
+         u.getEdgeDoFFunction().interpolate( real_t( 0 ), L, All );
+      }
+      else
+      {
+         Cloud                                      c( a.str( "src" ), h );
+         std::function< real_t( const Point3D& ) > fn = [&c]( const Point3D& p ) { return c( p ); };
+         q.interpolate( fn, L, All );
+         if ( comp == 0 )
+            P1ToP2ElementwiseBlendingDivTxOperator( st, L, L ).apply( q, u, L, flag, Replace );
+         else if ( comp == 1 )
+            P1ToP2ElementwiseBlendingDivTyOperator( st, L, L ).apply( q, u, L, flag, Replace );
+         else
+            P1ToP2ElementwiseBlendingDivTzOperator( st, L, L ).apply( q, u, L, flag, Replace );
+      }
+      dumpP2( u, L, a.str( "out" ), a.str( "oute" ) );
    }
    else if ( a.cmd == "p2restrict" || a.cmd == "p2prolongate" )
    {

@@ -148,3 +148,48 @@ def case_transfer(lib, kind, Lc):
     got = get(oc, Lc)
     assert rc.rel(got[m], g["%s_Lc%d_restrict" % (kind, Lc)][m]) < TOL
     assert np.array_equal(got[~m], xc[~m])  # DoFs of unselected primitives keep their values
+
+
+def case_div_blocks(lib, comp):
+    g = rc.gold_p2()
+    s = P2Setup(lib, "shell", 2)
+    x, d0 = rc.p2_inputs(s.o.n, 302)
+    u = s.fn("u", x)
+    q = api.P1Function("q", s.st, 2, 2)
+    api.P2ToP1ElementwiseBlendingDivOperator(s.st, 2, 2, comp).apply(u, q, 2, Inner)
+    got = s.o.p1.from_cells(q.download(2), 2, tol=1e-13)
+    m = (s.o.doftype[: s.o.nv] & 1) != 0
+    assert rc.rel(got[m], g["shell_L2_div_%d_inner" % comp][m]) < TOL
+    assert np.abs(got[~m]).max() == 0.0
+    q.upload(s.o.p1.to_cells(d0[: s.o.nv], 2), 2)
+    w = s.fn("w")
+    api.P1ToP2ElementwiseBlendingDivTOperator(s.st, 2, 2, comp).apply(q, w, 2, Inner)
+    m = s.o.mask(Inner)
+    assert rc.rel(s.get(w, tol=1e-13)[m], g["shell_L2_divt_%d_inner" % comp][m]) < TOL
+
+
+def case_stokes(lib):
+    """the fused vector epsilon kernel and the Taylor-Hood composite against the blocks of the oracle (each block pinned to the
+    reference: tests/test_p2_oracle_vs_reference.py)"""
+    s = P2Setup(lib, "shell", 2)
+    o = s.o
+    rng = np.random.default_rng(11)
+    U = [rng.random(o.n) - 0.5 for _ in range(3)]
+    pv = rng.random(o.nv) - 0.5
+    src, dst = api.P2P1TaylorHoodFunction("s", s.st, 2, 2), api.P2P1TaylorHoodFunction("d", s.st, 2, 2)
+    for c in range(3):
+        v, e = o.to_cells(U[c])
+        src.uvw[c].upload(v, e, 2)
+    src.p.upload(o.p1.to_cells(pv, 2), 2)
+    S = api.P2P1ElementwiseBlendingEpsilonStokesOperator(s.st, 2, 2, k_xyz)
+    S.apply(src, dst, 2, Inner)
+    m = o.mask(Inner)
+    B = [o.div_matrix(c) for c in range(3)]
+    for c in range(3):
+        want = sum(o.matrix(form="epsilon", comp=(c, d)) @ U[d] for d in range(3)) + B[c].T @ pv
+        got = s.get(dst.uvw[c], tol=1e-12)
+        assert rc.rel(got[m], want[m]) < 1e-11
+    wantp = sum(B[c] @ U[c] for c in range(3))
+    gotp = o.p1.from_cells(dst.p.download(2), 2, tol=1e-12)
+    mp = (o.doftype[: o.nv] & 1) != 0
+    assert rc.rel(gotp[mp], wantp[mp]) < 1e-11

@@ -32,6 +32,15 @@ def test_p2_blas(cuda_lib):
     pc.case_blas(cuda_lib)
 
 
-@pytest.mark.parametrize("kind,Lc", [("cube", 2), ("shell", 1), ("shell", 2)])
+@pytest.mark.parametrize("kind,Lc", [("cube", 2), ("shell", 1)])
 def test_quadratic_transfer(cuda_lib, kind, Lc):
-    pc.case_transfer(cuda_lib, kind, Lc) if (kind, Lc) != ("shell", 2) else None
+    pc.case_transfer(cuda_lib, kind, Lc)
+
+
+@pytest.mark.parametrize("comp", [0, 1, 2])
+def test_div_blocks(cuda_lib, comp):
+    pc.case_div_blocks(cuda_lib, comp)
+
+
+def test_stokes_composite(cuda_lib):
+    pc.case_stokes(cuda_lib)

@@ -30,3 +30,12 @@ def test_p2_blas(emul_lib):
 @pytest.mark.parametrize("kind,Lc", [("cube", 2), ("shell", 1)])
 def test_quadratic_transfer(emul_lib, kind, Lc):
     pc.case_transfer(emul_lib, kind, Lc)
+
+
+@pytest.mark.parametrize("comp", [0, 2])
+def test_div_blocks(emul_lib, comp):
+    pc.case_div_blocks(emul_lib, comp)
+
+
+def test_stokes_composite(emul_lib):
+    pc.case_stokes(emul_lib)

@@ -70,3 +70,16 @@ def test_quadratic_transfer(kind, Lc):
     assert rc.rel((P @ xc)[m], g["%s_Lc%d_prolongate" % (kind, Lc)][m]) < TOL
     m = oc.mask(5)
     assert rc.rel((P.T @ xf)[m], g["%s_Lc%d_restrict" % (kind, Lc)][m]) < TOL
+
+
+@pytest.mark.parametrize("comp", [0, 1, 2])
+def test_stokes_div_blocks(comp):
+    """B = P2ToP1ElementwiseBlendingDiv{x,y,z}Operator and B^T = P1ToP2ElementwiseBlendingDivT{x,y,z}Operator on the shell"""
+    g = rc.gold_p2()
+    o = rc.p2_oracle("shell", 2)
+    x, d0 = rc.p2_inputs(o.n, 302)
+    B = o.div_matrix(comp)
+    m = (o.doftype[: o.nv] & 1) != 0
+    assert rc.rel((B @ x)[m], g["shell_L2_div_%d_inner" % comp][m]) < TOL
+    m = o.mask(1)
+    assert rc.rel((B.T @ d0[: o.nv])[m], g["shell_L2_divt_%d_inner" % comp][m]) < TOL
