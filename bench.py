@@ -244,7 +244,7 @@ def main():
     (v, c), mesh_kind = workload_mesh(world, args.mesh)
     cell_rank = None
     if world > 1:
-        comm.init_nccl(lib)
+        comm.init_nccl(lib, segment_bytes=256 << 20)  # the shell's interfaces are whole spherical surfaces: several million doubles per pair at level 8
         if mesh_kind == "shell":
             cell_rank = meshes.partition_greedy(c, world)
     st = api.PrimitiveStorage(v, c, rank, world, cell_rank=cell_rank)
@@ -397,7 +397,10 @@ def main():
         for k in (0, 1):
             full, part = f1[k].download(Lc), fp[k].download(Lc)
             for i, gcell in enumerate(mine):
-                ok = ok and np.array_equal(full[gcell * csz:(gcell + 1) * csz], part[i * csz:(i + 1) * csz])
+                a_, b_ = full[gcell * csz:(gcell + 1) * csz], part[i * csz:(i + 1) * csz]
+                # k = 1: the apply result, bit for bit; k = 0: the iterate after one V-cycle -- its coarse-grid CG sums its dot
+                # products rank by rank, so the last bits may differ
+                ok = ok and (np.array_equal(a_, b_) if k == 1 else bool(np.abs(a_ - b_).max() <= 1e-12 * max(np.abs(a_).max(), 1e-300)))
         t = torch.tensor([1.0 if ok else 0.0], device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MIN)
         parity_ok = bool(t.item() > 0.5)
