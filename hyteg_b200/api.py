@@ -495,3 +495,27 @@ class P2P1ElementwiseBlendingEpsilonStokesOperator:
         for c in range(3):
             self.divT[c].apply(src.p, dst.uvw[c], level, flag, Add)
             self.div[c].apply(src.uvw[c], dst.p, level, flag, Replace if c == 0 else Add)
+
+
+class P2ChebyshevGMG:
+    """GeometricMultigridSolver< P2 elementwise operator > with ChebyshevSmoother, quadratic transfer and CG on the coarsest level"""
+
+    def __init__(self, storage, A, min_level, max_level, order, ev_guess, power_iterations=20, pre=2, post=2, coarse_max_iter=1000, coarse_tol=1e-14):
+        self.lib, self._keep = storage.lib, (storage, A, ev_guess)
+        self.h = self.lib.checkp(self.lib.dll.hb_p2_gmg_chebyshev_create(storage.h, A.h, min_level, max_level, order, ev_guess.h, power_iterations,
+                                                                         pre, post, coarse_max_iter, coarse_tol))
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.lib.dll.hb_p2solver_destroy(self.h)
+            self.h = None
+
+    @property
+    def spectral_radius(self):
+        return self.lib.dll.hb_p2solver_spectral_radius(self.h)
+
+    def solve(self, x, b, level):
+        self.lib.check(self.lib.dll.hb_p2solver_solve(self.h, x.h, b.h, level, 0))
+
+    def smooth(self, x, b, level):
+        self.lib.check(self.lib.dll.hb_p2solver_solve(self.h, x.h, b.h, level, 1))

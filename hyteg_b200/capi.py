@@ -113,6 +113,13 @@ _SIGNATURES = {
     "hb_p2operator_quadrature_points": (C.c_int, [_vp, C.c_int, _dp]),
     "hb_p2operator_set_sampled_coefficient": (C.c_int, [_vp, C.c_int, _dp]),
     "hb_p2operator_apply": (C.c_int, [_vp, _vp, _vp, C.c_int, C.c_int, C.c_int]),
+    "hb_p2function_mult_elementwise": (C.c_int, [_vp, C.c_int, C.POINTER(_vp), C.c_int, C.c_int]),
+    "hb_p2function_copy_boundary_condition": (C.c_int, [_vp, _vp]),
+    "hb_p2operator_diagonal": (C.c_int, [_vp, C.POINTER(_vp), C.c_int, C.c_int]),
+    "hb_p2_gmg_chebyshev_create": (_vp, [_vp, _vp, C.c_int, C.c_int, C.c_int, _vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_double]),
+    "hb_p2solver_spectral_radius": (C.c_double, [_vp]),
+    "hb_p2solver_solve": (C.c_int, [_vp, _vp, _vp, C.c_int, C.c_int]),
+    "hb_p2solver_destroy": (None, [_vp]),
     "hb_p2_div_create": (_vp, [_vp, C.c_int, C.c_int, C.c_int]),
     "hb_p2_divt_create": (_vp, [_vp, C.c_int, C.c_int, C.c_int]),
     "hb_p2_epsilon_vector_create": (_vp, [_vp, C.c_int, C.c_int, _vp]),

@@ -244,6 +244,44 @@ __global__ void hb_p2_elem_kernel( const HbP2View pv, const HbP2ElemArgs a )
                kval += kk[4 + k] * ( 4.0 * lam[hb_p2_pair[k][0]] * lam[hb_p2_pair[k][1]] );
          }
          const double s = Q[4] * kval * fabs( det );
+         if ( a.diagonal )
+         {
+            // A_ii = sum_q s |grad phi_i|^2 (+ s (d_c phi_i)^2 for the epsilon block (c,c) / component c of the vector operator)
+#pragma unroll
+            for ( int k = 0; k < 10; k++ )
+            {
+               double gh[3]; // gradhat phi_k
+               if ( k < 4 )
+               {
+                  const double f4 = 4.0 * lam[k] - 1.0;
+                  gh[0] = k == 0 ? -f4 : ( k == 1 ? f4 : 0.0 );
+                  gh[1] = k == 0 ? -f4 : ( k == 2 ? f4 : 0.0 );
+                  gh[2] = k == 0 ? -f4 : ( k == 3 ? f4 : 0.0 );
+               }
+               else
+               {
+                  const int pa = hb_p2_pair[k - 4][0], pb = hb_p2_pair[k - 4][1];
+#pragma unroll
+                  for ( int d = 0; d < 3; d++ )
+                  {
+                     const double ga = pa == 0 ? -1.0 : ( pa == d + 1 ? 1.0 : 0.0 ), gb = pb == 0 ? -1.0 : ( pb == d + 1 ? 1.0 : 0.0 );
+                     gh[d]           = 4.0 * ( lam[pa] * gb + lam[pb] * ga );
+                  }
+               }
+               double gp[3];
+#pragma unroll
+               for ( int d = 0; d < 3; d++ )
+                  gp[d] = Mi[d] * gh[0] + Mi[3 + d] * gh[1] + Mi[6 + d] * gh[2];
+               const double n2 = gp[0] * gp[0] + gp[1] * gp[1] + gp[2] * gp[2];
+#pragma unroll
+               for ( int cc = 0; cc < NC; cc++ )
+               {
+                  const int comp = NC == 3 ? cc : a.compC;
+                  yv[cc][k] += s * ( n2 + ( ( NC == 3 || a.form == HB_P2_EPSILON ) ? gp[comp] * gp[comp] : 0.0 ) );
+               }
+            }
+            continue;
+         }
          // physical gradient of every component: grad u = M^-T gradhat u, gradhat u from the coefficients c[k] of grad lambda_k
          double gu[NC][3];
          double pval = 0.0; // HB_P2_DIVT: the P1 source at the quadrature point
@@ -431,9 +469,21 @@ __global__ void hb_p2_edge_lincomb_kernel( const HbP2View pv, const HbP2LinComb 
    const int local = (int) ( i - (long long) cell * pv.eCellSize );
    if ( !( ( lc.selMask >> pv.cells[cell].region[pv.emask[local]].bflag ) & 1 ) )
       return;
-   double v = lc.shift + ( lc.accumulate ? lc.dst[i] : 0.0 );
-   for ( int k = 0; k < lc.n; k++ )
-      v += lc.c[k] * lc.src[k][i];
+   double v;
+   if ( lc.op == 1 )
+   {
+      v = 1.0;
+      for ( int k = 0; k < lc.n; k++ )
+         v *= lc.src[k][i];
+   }
+   else if ( lc.op == 2 )
+      v = 1.0 / lc.dst[i];
+   else
+   {
+      v = lc.shift + ( lc.accumulate ? lc.dst[i] : 0.0 );
+      for ( int k = 0; k < lc.n; k++ )
+         v += lc.c[k] * lc.src[k][i];
+   }
    lc.dst[i] = v;
 }
 

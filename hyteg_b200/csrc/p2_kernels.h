@@ -78,7 +78,7 @@ struct HbP2ElemArgs
    const double* kE;
    const double* kq;   // coefficient sampled at the quadrature points [cell][type][anchor][q] (or null; null and no kV: k = 1)
    int32_t       form, compC, compD;
-   int32_t       pad;
+   int32_t       diagonal; // 1: accumulate the operator's diagonal instead of A u (computeDiagonalOperatorValues)
 };
 
 struct HbP2FinalizeArgs
@@ -96,9 +96,10 @@ struct HbP2FinalizeArgs
    long long        nGroups;
 };
 
-// dst = sum_k c[k] src[k] (+ dst) on the edge DoFs selected by flag; also constants (n = 0, shift)
+// dst = sum_k c[k] src[k] (+ dst) on the edge DoFs selected by flag; also constants (n = 0, shift); op 1: dst = prod_k src[k]; op 2: dst = 1 / dst
 struct HbP2LinComb
 {
+   int32_t       op, pad0;
    double*       dst;
    const double* src[4];
    double        c[4];

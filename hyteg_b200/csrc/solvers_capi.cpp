@@ -5,6 +5,7 @@
 #include <string>
 
 #include "../../include/hyteg_b200/hyteg.hpp"
+#include "../../include/hyteg_b200/hyteg_p2.hpp"
 
 namespace hb {
 void setError( const std::string& s );
@@ -176,6 +177,67 @@ int hb_solver_solve( hb_solver* s, hb_operator* op, hb_function* x, hb_function*
    s->solver->solve( A, X, B, (hyteg::uint_t) level );
    return 0;
    HB_CATCH( 1 )
+}
+
+/* ---- P2: Chebyshev-smoothed GMG on an elementwise operator (the recipe of src/terraneo/solvers/StokesMCFGMRESSolver.hpp:71-143 for the
+ * velocity block: GeometricMultigridSolver + ChebyshevSmoother( inverse diagonal ) + quadratic transfer; CG on the coarsest level) ---- */
+struct hb_p2solver
+{
+   using P2Op = hyteg::P2ElementwiseOperatorB200;
+   StorageP                                                       storage;
+   std::shared_ptr< P2Op >                                        A;
+   std::shared_ptr< hyteg::ChebyshevSmoother< P2Op > >            cheb;
+   std::shared_ptr< hyteg::GeometricMultigridSolver< P2Op > >     gmg;
+   double                                                         rho = 0;
+   int                                                            minLevel = 0, maxLevel = 0;
+};
+
+hb_p2solver* hb_p2_gmg_chebyshev_create( hb_storage* st, hb_p2operator* op, int minLevel, int maxLevel, int order, hb_p2function* eigenvector_guess,
+                                         int powerIterations, int pre, int post, int coarseMaxIter, double coarseTol )
+{
+   HB_TRY
+   using P2Op = hb_p2solver::P2Op;
+   using P2Fn = hyteg::P2Function< double >;
+   auto s      = std::make_unique< hb_p2solver >();
+   s->storage  = borrow( st );
+   s->minLevel = minLevel;
+   s->maxLevel = maxLevel;
+   s->A        = std::make_shared< P2Op >( op, s->storage, (hyteg::uint_t) minLevel, (hyteg::uint_t) maxLevel );
+   s->A->computeInverseDiagonalOperatorValues();
+   P2Fn ev( eigenvector_guess, s->storage, (hyteg::uint_t) maxLevel, (hyteg::uint_t) maxLevel );
+   P2Fn tmp( "tmp", s->storage, (hyteg::uint_t) maxLevel, (hyteg::uint_t) maxLevel );
+   s->rho  = hyteg::chebyshev::estimateRadius( *s->A, (hyteg::uint_t) maxLevel, (hyteg::uint_t) powerIterations, s->storage, ev, tmp );
+   s->cheb = std::make_shared< hyteg::ChebyshevSmoother< P2Op > >( s->storage, minLevel, maxLevel );
+   s->cheb->setupCoefficients( (hyteg::uint_t) order, s->rho );
+   auto coarse = std::make_shared< hyteg::CGSolver< P2Op > >( s->storage, minLevel, minLevel, (hyteg::uint_t) coarseMaxIter, coarseTol, coarseTol );
+   s->gmg      = std::make_shared< hyteg::GeometricMultigridSolver< P2Op > >( s->storage, s->cheb, coarse, std::make_shared< hyteg::P2toP2QuadraticRestriction >(),
+                                                                              std::make_shared< hyteg::P2toP2QuadraticProlongation >(), minLevel, maxLevel, pre, post );
+   return s.release();
+   HB_CATCH( nullptr )
+}
+
+double hb_p2solver_spectral_radius( const hb_p2solver* s )
+{
+   return s->rho;
+}
+
+/* what = 0: one V-cycle (GeometricMultigridSolver::solve), 1: one call of the Chebyshev smoother on 'level' */
+int hb_p2solver_solve( hb_p2solver* s, hb_p2function* x, hb_p2function* b, int level, int what )
+{
+   HB_TRY
+   using P2Fn = hyteg::P2Function< double >;
+   P2Fn X( x, s->storage, (hyteg::uint_t) s->minLevel, (hyteg::uint_t) s->maxLevel ), B( b, s->storage, (hyteg::uint_t) s->minLevel, (hyteg::uint_t) s->maxLevel );
+   if ( what == 1 )
+      s->cheb->solve( *s->A, X, B, (hyteg::uint_t) level );
+   else
+      s->gmg->solve( *s->A, X, B, (hyteg::uint_t) level );
+   return 0;
+   HB_CATCH( 1 )
+}
+
+void hb_p2solver_destroy( hb_p2solver* s )
+{
+   delete s;
 }
 
 int hb_solver_iterations( const hb_solver* s )

@@ -227,6 +227,8 @@ int hb_p2function_interpolate_constant( hb_p2function* f, double value, int leve
 int hb_p2function_assign( hb_p2function* dst, int n, const double* scalars, hb_p2function* const* srcs, int level, int flag );
 int hb_p2function_add( hb_p2function* dst, int n, const double* scalars, hb_p2function* const* srcs, int level, int flag );
 int hb_p2function_dot( const hb_p2function* a, const hb_p2function* b, int level, int flag, double* out );
+int hb_p2function_mult_elementwise( hb_p2function* dst, int n, hb_p2function* const* srcs, int level, int flag );
+int hb_p2function_copy_boundary_condition( hb_p2function* dst, const hb_p2function* src );
 
 /* P2ElementwiseOperator< forms::p2_div_k_grad_blending_q4 > (P2ElementwiseBlendingDivKGradOperator, P2ElementwiseOperator.hpp:475) /
  * operatorgeneration::P2ElementwiseDivKGrad...: k as a P2Function (the hyteg_operators way; null: k = 1), or sampled at the quadrature
@@ -243,6 +245,9 @@ int            hb_p2operator_set_sampled_coefficient( hb_p2operator* op, int lev
 /* Operator::apply( src, dst, level, flag, updateType ) -- P2ElementwiseOperator::gemv (P2ElementwiseOperator.cpp:109-330) */
 int hb_p2operator_apply( hb_p2operator* op, const hb_p2function* src, hb_p2function* dst, int level, int flag, int update_type );
 
+/* computeDiagonalOperatorValues / computeInverseDiagonalOperatorValues (P2ElementwiseOperator.cpp:332-420): f has one entry, three
+ * for the vector epsilon operator */
+int hb_p2operator_diagonal( hb_p2operator* op, hb_p2function* const* f, int level, int inverse );
 /* P2ToP1ElementwiseBlendingDiv{x,y,z}Operator (P2ToP1ElementwiseOperator.hpp:264-266, forms::p2_to_p1_div_c_blending_q2) and
  * P1ToP2ElementwiseBlendingDivT{x,y,z}Operator (P1ToP2ElementwiseOperator.hpp:275-277, forms::p1_to_p2_divt_c_blending_q2): the B and
  * B^T blocks of P2P1ElementwiseBlendingStokesOperator (P2P1ElementwiseBlendingStokesOperator.hpp:91-100); component 0..2 */
@@ -254,6 +259,17 @@ int hb_p2operator_apply_p1_to_p2( hb_p2operator* op, const hb_function* src, hb_
  * function (three P2Functions), the geometry of a quadrature point evaluated once */
 hb_p2operator* hb_p2_epsilon_vector_create( hb_storage* st, int min_level, int max_level, const hb_p2function* mu );
 int hb_p2operator_apply_vector( hb_p2operator* op, hb_p2function* const* src3, hb_p2function* const* dst3, int level, int flag, int update_type );
+
+/* Chebyshev-smoothed geometric multigrid on a P2 elementwise operator (BASELINE config 4; the velocity-block recipe of
+ * src/terraneo/solvers/StokesMCFGMRESSolver.hpp:71-143): GeometricMultigridSolver + ChebyshevSmoother with the inverse diagonal
+ * (radius from power iterations started at eigenvector_guess on max_level, ChebyshevSmoother.hpp:655-665) + quadratic transfer, CG on
+ * min_level.  what = 0: one V(pre,post) cycle, 1: one call of the smoother. */
+typedef struct hb_p2solver hb_p2solver;
+hb_p2solver* hb_p2_gmg_chebyshev_create( hb_storage* st, hb_p2operator* op, int min_level, int max_level, int order, hb_p2function* eigenvector_guess,
+                                         int power_iterations, int pre, int post, int coarse_max_iter, double coarse_tol );
+double       hb_p2solver_spectral_radius( const hb_p2solver* s );
+int          hb_p2solver_solve( hb_p2solver* s, hb_p2function* x, hb_p2function* b, int level, int what );
+void         hb_p2solver_destroy( hb_p2solver* s );
 
 /* P2toP2QuadraticRestriction::restrict / P2toP2QuadraticProlongation::prolongate / prolongateAndAdd
  * (src/hyteg/gridtransferoperators/P2toP2QuadraticRestriction.cpp:131-251, P2toP2QuadraticProlongation.cpp) */

@@ -33,7 +33,21 @@ class P2Function
    , f_( hbCheckPtr( hb_p2function_create( storage->handle(), (int) minLevel, (int) maxLevel ) ) )
    , v_( hb_p2function_vertex_part( f_ ), storage, minLevel, maxLevel )
    {}
-   ~P2Function() { hb_p2function_destroy( f_ ); }
+   /// non-owning view of an existing C-ABI handle
+   P2Function( hb_p2function* borrowed, const std::shared_ptr< PrimitiveStorage >& storage, uint_t minLevel, uint_t maxLevel )
+   : name_( "borrowed" )
+   , storage_( storage )
+   , minLevel_( minLevel )
+   , maxLevel_( maxLevel )
+   , f_( borrowed )
+   , v_( hb_p2function_vertex_part( f_ ), storage, minLevel, maxLevel )
+   , owned_( false )
+   {}
+   ~P2Function()
+   {
+      if ( owned_ )
+         hb_p2function_destroy( f_ );
+   }
    P2Function( const P2Function& )            = delete;
    P2Function& operator=( const P2Function& ) = delete;
 
@@ -107,6 +121,15 @@ class P2Function
       hbCheck( hb_p2function_dot( f_, rhs.f_, (int) level, (int) flag, &v ) );
       return v;
    }
+   void multElementwise( const std::vector< std::reference_wrapper< const P2Function > >& functions, uint_t level, DoFType flag = All ) const
+   {
+      std::vector< hb_p2function* > h;
+      for ( const P2Function& f : functions )
+         h.push_back( f.f_ );
+      hbCheck( hb_p2function_mult_elementwise( f_, (int) h.size(), h.data(), (int) level, (int) flag ) );
+   }
+   void setToZero( uint_t level ) const { interpolate( ValueType( 0 ), level, All ); }
+   void copyBoundaryConditionFromFunction( const P2Function& other ) const { hbCheck( hb_p2function_copy_boundary_condition( f_, other.f_ ) ); }
 
  private:
    std::string                         name_;
@@ -114,6 +137,7 @@ class P2Function
    uint_t                              minLevel_, maxLevel_;
    hb_p2function*                      f_;
    P1Function< ValueType >             v_; // non-owning view of the vertex part
+   bool                                owned_ = true;
 };
 
 /// P2ElementwiseOperator< Form > for the forms of the fused path; the coefficient is a P2Function (the hyteg_operators interface), a host
@@ -123,16 +147,65 @@ class P2ElementwiseOperatorB200
  public:
    using srcType = P2Function< real_t >;
    using dstType = P2Function< real_t >;
-   virtual ~P2ElementwiseOperatorB200() { hb_p2operator_destroy( op_ ); }
+   /// non-owning view of an existing C-ABI handle
+   P2ElementwiseOperatorB200( hb_p2operator* borrowed, const std::shared_ptr< PrimitiveStorage >& storage, uint_t minLevel, uint_t maxLevel )
+   : op_( borrowed )
+   , owned_( false )
+   , storage_( storage )
+   , minLevel_( minLevel )
+   , maxLevel_( maxLevel )
+   {}
+   virtual ~P2ElementwiseOperatorB200()
+   {
+      if ( owned_ )
+         hb_p2operator_destroy( op_ );
+   }
    void apply( const srcType& src, const dstType& dst, size_t level, DoFType flag, UpdateType updateType = Replace ) const
    {
       hbCheck( hb_p2operator_apply( op_, src.handle(), dst.handle(), (int) level, (int) flag, (int) updateType ) );
    }
    hb_p2operator* handle() const { return op_; }
+   /// OperatorWithInverseDiagonal (P2ElementwiseOperator.hpp:133-160)
+   void computeInverseDiagonalOperatorValues()
+   {
+      invDiag_ = std::make_shared< srcType >( "inverse diagonal entries", storage_, minLevel_, maxLevel_ );
+      for ( uint_t l = minLevel_; l <= maxLevel_; l++ )
+      {
+         hb_p2function* f = invDiag_->handle();
+         hbCheck( hb_p2operator_diagonal( op_, &f, (int) l, 1 ) );
+      }
+   }
+   std::shared_ptr< srcType > getInverseDiagonalValues() const
+   {
+      if ( !invDiag_ )
+         throw std::runtime_error( "Inverse diagonal values have not been assembled, call computeInverseDiagonalOperatorValues() to set up this function." );
+      return invDiag_;
+   }
+   // the building blocks the solver templates (hyteg_solvers.hpp) call; here chains of apply + BLAS-1 like in the reference
+   void residual( const srcType& x, const srcType& b, const srcType& r, size_t level, DoFType flag ) const
+   {
+      apply( x, r, level, flag, Replace );
+      r.assign( { 1.0, -1.0 }, { b, r }, level, flag );
+   }
+   void chebFirst( const srcType& x, const srcType& b, const srcType& dst, size_t level, DoFType flag ) const
+   {
+      residual( x, b, dst, level, flag );
+      dst.multElementwise( { *getInverseDiagonalValues(), dst }, level, flag );
+   }
+   void chebStep( const srcType& src, const srcType& dst, const srcType& x, real_t coeff, size_t level, DoFType flag ) const
+   {
+      apply( src, dst, level, flag, Replace );
+      dst.multElementwise( { *getInverseDiagonalValues(), dst }, level, flag );
+      x.add( { coeff }, { src }, level, flag );
+   }
 
  protected:
-   P2ElementwiseOperatorB200( hb_p2operator* op, uint_t minLevel, uint_t maxLevel, const std::function< real_t( const Point3D& ) >* k )
+   P2ElementwiseOperatorB200( hb_p2operator* op, const std::shared_ptr< PrimitiveStorage >& storage, uint_t minLevel, uint_t maxLevel,
+                              const std::function< real_t( const Point3D& ) >* k )
    : op_( hbCheckPtr( op ) )
+   , storage_( storage )
+   , minLevel_( minLevel )
+   , maxLevel_( maxLevel )
    {
       if ( k )
          for ( uint_t L = minLevel; L <= maxLevel; L++ )
@@ -145,7 +218,11 @@ class P2ElementwiseOperatorB200
             hbCheck( hb_p2operator_set_sampled_coefficient( op_, (int) L, val.data() ) );
          }
    }
-   hb_p2operator* op_;
+   hb_p2operator*                      op_;
+   bool                                owned_ = true;
+   std::shared_ptr< PrimitiveStorage > storage_;
+   uint_t                              minLevel_ = 0, maxLevel_ = 0;
+   std::shared_ptr< srcType >          invDiag_;
 };
 
 /// P2ElementwiseBlendingDivKGradOperator (P2ElementwiseOperator.hpp:475) / operatorgeneration::P2ElementwiseDivKGrad...
@@ -153,10 +230,10 @@ class P2ElementwiseBlendingDivKGradOperator : public P2ElementwiseOperatorB200
 {
  public:
    P2ElementwiseBlendingDivKGradOperator( const std::shared_ptr< PrimitiveStorage >& storage, size_t minLevel, size_t maxLevel, const P2Function< real_t >& k )
-   : P2ElementwiseOperatorB200( hb_p2_divkgrad_create( storage->handle(), (int) minLevel, (int) maxLevel, k.handle() ), minLevel, maxLevel, nullptr )
+   : P2ElementwiseOperatorB200( hb_p2_divkgrad_create( storage->handle(), (int) minLevel, (int) maxLevel, k.handle() ), storage, minLevel, maxLevel, nullptr )
    {}
    P2ElementwiseBlendingDivKGradOperator( const std::shared_ptr< PrimitiveStorage >& storage, size_t minLevel, size_t maxLevel, const std::function< real_t( const Point3D& ) >& k )
-   : P2ElementwiseOperatorB200( hb_p2_divkgrad_create( storage->handle(), (int) minLevel, (int) maxLevel, nullptr ), minLevel, maxLevel, &k )
+   : P2ElementwiseOperatorB200( hb_p2_divkgrad_create( storage->handle(), (int) minLevel, (int) maxLevel, nullptr ), storage, minLevel, maxLevel, &k )
    {}
 };
 
@@ -165,11 +242,33 @@ class P2ElementwiseBlendingEpsilonBlock : public P2ElementwiseOperatorB200
 {
  public:
    P2ElementwiseBlendingEpsilonBlock( const std::shared_ptr< PrimitiveStorage >& storage, size_t minLevel, size_t maxLevel, int i, int j, const std::function< real_t( const Point3D& ) >& mu )
-   : P2ElementwiseOperatorB200( hb_p2_epsilon_create( storage->handle(), (int) minLevel, (int) maxLevel, i, j, nullptr ), minLevel, maxLevel, &mu )
+   : P2ElementwiseOperatorB200( hb_p2_epsilon_create( storage->handle(), (int) minLevel, (int) maxLevel, i, j, nullptr ), storage, minLevel, maxLevel, &mu )
    {}
    P2ElementwiseBlendingEpsilonBlock( const std::shared_ptr< PrimitiveStorage >& storage, size_t minLevel, size_t maxLevel, int i, int j, const P2Function< real_t >& mu )
-   : P2ElementwiseOperatorB200( hb_p2_epsilon_create( storage->handle(), (int) minLevel, (int) maxLevel, i, j, mu.handle() ), minLevel, maxLevel, nullptr )
+   : P2ElementwiseOperatorB200( hb_p2_epsilon_create( storage->handle(), (int) minLevel, (int) maxLevel, i, j, mu.handle() ), storage, minLevel, maxLevel, nullptr )
    {}
+};
+
+/// gridtransferoperators/P2toP2QuadraticRestriction.hpp / P2toP2QuadraticProlongation.hpp
+class P2toP2QuadraticRestriction : public RestrictionOperator< P2Function< real_t > >
+{
+ public:
+   void restrict( const P2Function< real_t >& function, const uint_t& sourceLevel, const DoFType& flag ) const override
+   {
+      hbCheck( hb_p2_restrict( function.handle(), (int) sourceLevel, (int) flag ) );
+   }
+};
+class P2toP2QuadraticProlongation : public ProlongationOperator< P2Function< real_t > >
+{
+ public:
+   void prolongate( const P2Function< real_t >& function, const uint_t& sourceLevel, const DoFType& flag ) const override
+   {
+      hbCheck( hb_p2_prolongate( function.handle(), (int) sourceLevel, (int) flag ) );
+   }
+   void prolongateAndAdd( const P2Function< real_t >& function, const uint_t& sourceLevel, const DoFType& flag ) const override
+   {
+      hbCheck( hb_p2_prolongate_and_add( function.handle(), (int) sourceLevel, (int) flag ) );
+   }
 };
 
 } // namespace hyteg

@@ -50,6 +50,26 @@ def main():
         _, cl = s.run("p2fromp1", 2, src=s.cloud(phys[: o.nv], d0[: o.nv]), oute=oute, comp=comp, flag=1, shell=1)
         de = np.fromfile(oute).reshape(-1, 4)
         out["shell_L2_divt_%d_inner" % comp] = np.concatenate([rb.to_global(o.xyz[: o.nv], cl, tol), rb.to_global(o.xyz[o.nv:], (de[:, :3], de[:, 3]), tol)])
+    # Chebyshev smoother and the Chebyshev-smoothed GMG on the blended div-k-grad operator (levels 1..3, V(2,2), order 3, CG on level 1)
+    o = p2.P2Oracle(v, c, 3, shell=True)
+    rng = np.random.default_rng(9)
+    x0, b, ev = rng.random(o.n), rng.random(o.n) - 0.5, rng.random(o.n)
+    phys = o.dof_physical_coordinates()
+    cx, cb, cev = s.cloud(phys, x0), s.cloud(phys, b), s.cloud(phys, ev)
+    tol = 0.05 * rb.min_spacing(v, c, 3)
+
+    def getp2(cl, oute):
+        de = np.fromfile(oute).reshape(-1, 4)
+        return np.concatenate([rb.to_global(o.xyz[: o.nv], cl, tol), rb.to_global(o.xyz[o.nv:], (de[:, :3], de[:, 3]), tol)])
+
+    oute = os.path.join(s.dir, "ge.bin")
+    r, cl = s.run("p2cheb", 3, minlevel=3, x=cx, rhs=cb, ev=cev, order=3, sweeps=2, shell=1, oute=oute)
+    out["shell_L3_cheb3_2sweeps"] = getp2(cl, oute)
+    out["shell_L3_rho20"] = np.array(r["rho"])
+    r, cl = s.run("p2gmg", 3, minlevel=1, x=cx, rhs=cb, ev=cev, order=3, cycles=5, pre=2, post=2, shell=1, oute=oute)
+    out["shell_gmg_cheb_res2"] = np.array(r["res2"])
+    out["shell_gmg_cheb_x"] = getp2(cl, oute)
+    print("P2 GMG done", flush=True)
     # IcosahedralShellMap samples per macro-cell (cells identified by their centroid)
     for nt, nr in ((3, 2), (2, 3)):
         vv, cc = meshes.spherical_shell(nt, nr, 0.5, 1.0)

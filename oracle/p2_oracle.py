@@ -388,3 +388,85 @@ def quadratic_prolongation(coarse, fine, tol=1e-9):
     P = sp.csr_matrix((vals[first], (rows[first], cols[first])), shape=(fine.n, coarse.n))
     P.eliminate_zeros()
     return P
+
+
+# ---- smoothers and multigrid on assembled P2 operators (same algorithms as oracle/p1_oracle.py, on matrices) ----------------------------
+
+SMOOTH_FLAG = po.SMOOTH_FLAG
+
+
+def estimate_radius(M, x, iters):
+    """chebyshev::estimateRadius: power iteration on D^-1 A, flag All (numerictools/SpectrumEstimation.hpp:56-85)"""
+    d = M.diagonal()
+    op = lambda v: (M @ v) / d
+    x = x / np.sqrt(x @ x)
+    aux = op(x)
+    radius = 0.0
+    for _ in range(iters):
+        x = aux / np.sqrt(aux @ aux)
+        aux = op(x)
+        radius = x @ aux
+    return radius
+
+
+def chebyshev(o, M, x, b, coeffs, flag=SMOOTH_FLAG):
+    """ChebyshevSmoother::solve (solvers/ChebyshevSmoother.hpp:179-222) with the inverse diagonal as preconditioner"""
+    m = o.mask(flag)
+    d = M.diagonal()
+    x = x.copy()
+    tmp1 = np.zeros(o.n)
+    tmp1[m] = ((b - M @ x) / d)[m]
+    x[m] += coeffs[0] * tmp1[m]
+    for k in range(1, len(coeffs)):
+        t = np.zeros(o.n)
+        t[m] = ((M @ tmp1) / d)[m]
+        tmp1 = t
+        x[m] += coeffs[k] * tmp1[m]
+    return x
+
+
+def cg(o, M, x, b, max_iter, rel_tol, abs_tol, flag=SMOOTH_FLAG):
+    m = o.mask(flag)
+    x = x.copy()
+    r = np.zeros(o.n)
+    r[m] = (b - M @ x)[m]
+    p = r.copy()
+    rs = r @ r
+    r0 = np.sqrt(rs)
+    if r0 < abs_tol:
+        return x
+    for _ in range(max_iter):
+        ap = np.zeros(o.n)
+        ap[m] = (M @ p)[m]
+        alpha = rs / (p @ ap)
+        x[m] += alpha * p[m]
+        r[m] -= alpha * ap[m]
+        rn = r @ r
+        if np.sqrt(rn) / r0 < rel_tol or np.sqrt(rn) < abs_tol:
+            break
+        p = r + (rn / rs) * p
+        rs = rn
+    return x
+
+
+def vcycle(os_, Ms, Ps, coeffs, x, b, L, min_level, pre, post, flag=SMOOTH_FLAG):
+    """GeometricMultigridSolver::solveRecursively (solvers/GeometricMultigridSolver.hpp:207-312) with the Chebyshev smoother,
+    quadratic transfer (Ps[l]: level l-1 -> l) and CG (1e-14, at most 1000 iterations) on min_level; dicts indexed by level"""
+    o, M = os_[L], Ms[L]
+    if L == min_level:
+        x[L] = cg(o, M, x[L], b[L], 1000, 1e-14, 1e-14)
+        return
+    for _ in range(pre):
+        x[L] = chebyshev(o, M, x[L], b[L], coeffs)
+    m = o.mask(flag)
+    tmp = np.zeros(o.n)
+    tmp[m] = (b[L] - M @ x[L])[m]
+    mc = os_[L - 1].mask(flag)
+    rc_ = b[L - 1].copy()
+    rc_[mc] = (Ps[L].T @ tmp)[mc]
+    b[L - 1] = rc_
+    x[L - 1] = np.zeros(os_[L - 1].n)
+    vcycle(os_, Ms, Ps, coeffs, x, b, L - 1, min_level, pre, post, flag)
+    x[L][m] += (Ps[L] @ x[L - 1])[m]
+    for _ in range(post):
+        x[L] = chebyshev(o, M, x[L], b[L], coeffs)

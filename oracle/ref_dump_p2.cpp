@@ -24,6 +24,9 @@
 #include "hyteg/gridtransferoperators/P2toP2QuadraticRestriction.hpp"
 #include "hyteg/p1functionspace/VertexDoFMacroCell.hpp"
 #include "hyteg/p2functionspace/P2Function.hpp"
+#include "hyteg/solvers/CGSolver.hpp"
+#include "hyteg/solvers/ChebyshevSmoother.hpp"
+#include "hyteg/solvers/GeometricMultigridSolver.hpp"
 
 using namespace hyteg;
 using walberla::real_t;
@@ -173,6 +176,51 @@ int mainP2( const Args& a )
             P1ToP2ElementwiseBlendingDivTzOperator( st, L, L ).apply( q, u, L, flag, Replace );
       }
       dumpP2( u, L, a.str( "out" ), a.str( "oute" ) );
+   }
+   else if ( a.cmd == "p2gmg" || a.cmd == "p2cheb" )
+   {
+      // TerraNeo-style recipe on the scalar blended div-k-grad operator: GeometricMultigridSolver with ChebyshevSmoother (inverse
+      // diagonal, radius from power iterations on the finest level), CG on the coarsest level, quadratic transfer
+      using OpT           = P2ElementwiseOperator< forms::p2_div_k_grad_blending_q4 >;
+      const uint_t minL   = uint_t( a.num( "minlevel", 1 ) );
+      forms::p2_div_k_grad_blending_q4 f( coefficientK, coefficientK );
+      OpT                              A( st, minL, L, f );
+      A.computeInverseDiagonalOperatorValues();
+      P2Function< real_t > x( "x", st, minL, L ), b( "b", st, minL, L ), r( "r", st, minL, L ), ev( "ev", st, minL, L ), tmp( "tmp", st, minL, L ),
+          one( "one", st, minL, L );
+      setP2FromCloud( x, a.str( "x" ), h, L );
+      setP2FromCloud( b, a.str( "rhs" ), h, L );
+      setP2FromCloud( ev, a.str( "ev" ), h, L );
+      one.interpolate( real_t( 1 ), L, All );
+      const double npts = one.dotGlobal( one, L, Inner );
+      const double rho  = chebyshev::estimateRadius( A, L, uint_t( a.num( "power_iterations", 20 ) ), st, ev, tmp );
+      std::printf( "RESULT rho %.17g\n", rho );
+      auto cheb = std::make_shared< ChebyshevSmoother< OpT > >( st, minL, L );
+      cheb->setupCoefficients( uint_t( a.num( "order", 3 ) ), rho );
+      auto res2 = [&]() {
+         A.apply( x, r, L, Inner );
+         r.assign( { 1.0, -1.0 }, { b, r }, L, Inner );
+         return r.dotGlobal( r, L, Inner ) / npts;
+      };
+      if ( a.cmd == "p2cheb" )
+      {
+         for ( int k = 0; k < int( a.num( "sweeps", 1 ) ); k++ )
+            cheb->solve( A, x, b, L );
+      }
+      else
+      {
+         auto coarse = std::make_shared< CGSolver< OpT > >( st, minL, minL, 1000, 1e-14, 1e-14 );
+         auto R      = std::make_shared< P2toP2QuadraticRestriction >();
+         auto P      = std::make_shared< P2toP2QuadraticProlongation >();
+         GeometricMultigridSolver< OpT > gmg( st, cheb, coarse, R, P, minL, L, uint_t( a.num( "pre", 2 ) ), uint_t( a.num( "post", 2 ) ) );
+         std::printf( "RESULT res2 %.17g\n", res2() );
+         for ( int c = 0; c < int( a.num( "cycles", 5 ) ); c++ )
+         {
+            gmg.solve( A, x, b, L );
+            std::printf( "RESULT res2 %.17g\n", res2() );
+         }
+      }
+      dumpP2( x, L, a.str( "out" ), a.str( "oute" ) );
    }
    else if ( a.cmd == "p2restrict" || a.cmd == "p2prolongate" )
    {

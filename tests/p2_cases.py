@@ -193,3 +193,49 @@ def case_stokes(lib):
     gotp = o.p1.from_cells(dst.p.download(2), 2, tol=1e-12)
     mp = (o.doftype[: o.nv] & 1) != 0
     assert rc.rel(gotp[mp], wantp[mp]) < 1e-11
+
+
+def case_chebyshev_gmg(lib, cycles=5):
+    """Chebyshev smoother (order 3, inverse diagonal) and the Chebyshev-smoothed V(2,2) GMG, levels 1..3 on the blended shell, against
+    the REFERENCE's own run of GeometricMultigridSolver< P2ElementwiseOperator< p2_div_k_grad_blending_q4 > > (tests/golden/ref_p2.npz)"""
+    g = rc.gold_p2()
+    v, c = meshes.spherical_shell(*rc.SHELL)
+    o = rc.p2_oracle("shell", 3)
+    st = api.PrimitiveStorage(v, c, lib=lib)
+    st.setMeshBoundaryFlagsOnBoundary(1, 0, True)
+    api.setIcosahedralShellMap(st)
+    rng = np.random.default_rng(9)
+    x0, b, ev = rng.random(o.n), rng.random(o.n) - 0.5, rng.random(o.n)
+
+    def fn(name, val=None):
+        f = api.P2Function(name, st, 1, 3)
+        if val is not None:
+            vv, ee = o.to_cells(val)
+            f.upload(vv, ee, 3)
+        return f
+
+    def get(f):
+        vv, ee = f.download(3)
+        return o.from_cells(vv, ee, tol=1e-12)
+
+    A = api.P2ElementwiseBlendingDivKGradOperator(st, 1, 3, k_xyz)
+    x, rhs, fev = fn("x", x0), fn("b", b), fn("ev", ev)
+    S = api.P2ChebyshevGMG(st, A, 1, 3, 3, fev, power_iterations=20, pre=2, post=2)
+    assert abs(S.spectral_radius - g["shell_L3_rho20"][0]) < 1e-10 * S.spectral_radius
+    S.smooth(x, rhs, 3)
+    S.smooth(x, rhs, 3)
+    assert rc.rel(get(x), g["shell_L3_cheb3_2sweeps"]) < 1e-11
+    x = fn("x", x0)
+    r = fn("r")
+    m = o.mask(Inner)
+    res = []
+    for k in range(cycles + 1):
+        A.apply(x, r, 3, Inner)
+        r.assign([1.0, -1.0], [rhs, r], 3, Inner)
+        res.append(r.dotGlobal(r, 3, Inner) / m.sum())
+        if k < cycles:
+            S.solve(x, rhs, 3)
+    want = g["shell_gmg_cheb_res2"]
+    assert np.allclose(res, want[: cycles + 1], rtol=1e-7), (res, want)
+    if cycles == 5:
+        assert rc.rel(get(x), g["shell_gmg_cheb_x"]) < 1e-9

@@ -44,3 +44,7 @@ def test_div_blocks(cuda_lib, comp):
 
 def test_stokes_composite(cuda_lib):
     pc.case_stokes(cuda_lib)
+
+
+def test_chebyshev_gmg_matches_reference(cuda_lib):
+    pc.case_chebyshev_gmg(cuda_lib)

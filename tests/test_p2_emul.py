@@ -39,3 +39,7 @@ def test_div_blocks(emul_lib, comp):
 
 def test_stokes_composite(emul_lib):
     pc.case_stokes(emul_lib)
+
+
+def test_chebyshev_gmg(emul_lib):
+    pc.case_chebyshev_gmg(emul_lib, cycles=2)
