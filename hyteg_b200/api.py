@@ -484,13 +484,21 @@ class P2P1ElementwiseBlendingEpsilonStokesOperator:
     P2P1ElementwiseBlendingStokesOperator::apply (elementwiseoperators/P2P1ElementwiseBlendingStokesOperator.hpp:91-100) with
     P2ElementwiseBlendingEpsilonOperator as A (BASELINE config 4; src/hyteg_operators_composites/stokes/P2P1StokesEpsilonOperator.hpp)"""
 
-    def __init__(self, storage, min_level, max_level, mu=None):
+    def __init__(self, storage, min_level, max_level, mu=None, fused=True):
         self.A = P2ElementwiseBlendingEpsilonOperator(storage, min_level, max_level, mu)
         self.div = [P2ToP1ElementwiseBlendingDivOperator(storage, min_level, max_level, c) for c in range(3)]
         self.divT = [P1ToP2ElementwiseBlendingDivTOperator(storage, min_level, max_level, c) for c in range(3)]
+        # one kernel for A u + B^T p and B u: the geometry of a quadrature point is evaluated once instead of seven times
+        kh = mu.h if isinstance(mu, P2Function) else None
+        self.fused = P2ElementwiseOperator(storage, min_level, max_level, storage.lib.dll.hb_p2_stokes_create(storage.h, min_level, max_level, kh), mu) if fused else None
 
     def apply(self, src, dst, level, flag, update=Replace):
         assert update == Replace
+        if self.fused is not None:
+            hs = (C.c_void_p * 3)(*[f.h for f in src.uvw])
+            hd = (C.c_void_p * 3)(*[f.h for f in dst.uvw])
+            self.fused.lib.check(self.fused.lib.dll.hb_p2operator_apply_stokes(self.fused.h, hs, src.p.h, hd, dst.p.h, level, flag))
+            return
         self.A.apply(src.uvw, dst.uvw, level, flag, Replace)
         for c in range(3):
             self.divT[c].apply(src.p, dst.uvw[c], level, flag, Add)

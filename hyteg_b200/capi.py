@@ -120,6 +120,8 @@ _SIGNATURES = {
     "hb_p2solver_spectral_radius": (C.c_double, [_vp]),
     "hb_p2solver_solve": (C.c_int, [_vp, _vp, _vp, C.c_int, C.c_int]),
     "hb_p2solver_destroy": (None, [_vp]),
+    "hb_p2_stokes_create": (_vp, [_vp, C.c_int, C.c_int, _vp]),
+    "hb_p2operator_apply_stokes": (C.c_int, [_vp, C.POINTER(_vp), _vp, C.POINTER(_vp), _vp, C.c_int, C.c_int]),
     "hb_p2_div_create": (_vp, [_vp, C.c_int, C.c_int, C.c_int]),
     "hb_p2_divt_create": (_vp, [_vp, C.c_int, C.c_int, C.c_int]),
     "hb_p2_epsilon_vector_create": (_vp, [_vp, C.c_int, C.c_int, _vp]),

@@ -154,13 +154,14 @@ __global__ void hb_p2_elem_kernel( const HbP2View pv, const HbP2ElemArgs a )
    const bool         q2   = hb_p2_form_q2( a.form );
    const int          nq   = q2 ? 4 : 11;
    const bool         p1In = a.form == HB_P2_DIVT, p1Out = a.form == HB_P2_DIV;
+   const bool         stokes = NC == 3 && a.form == HB_P2_STOKES;
    for ( int t = 0; t < 6; t++ )
    {
       if ( x + y + z > N - hb_p2_slack[t] )
          continue;
       // local DoFs
       int    vi[4], ei[6];
-      double X[4][3], u[NC][10], kk[10];
+      double X[4][3], u[NC][10], kk[10], pk[4], yp[4];
 #pragma unroll
       for ( int k = 0; k < 4; k++ )
       {
@@ -170,6 +171,8 @@ __global__ void hb_p2_elem_kernel( const HbP2View pv, const HbP2ElemArgs a )
 #pragma unroll
          for ( int c = 0; c < NC; c++ )
             u[c][k] = a.srcV[c][vb + vi[k]];
+         pk[k] = stokes ? a.srcP[vb + vi[k]] : 0.0;
+         yp[k] = 0.0;
       }
 #pragma unroll
       for ( int k = 0; k < 6; k++ )
@@ -312,6 +315,18 @@ __global__ void hb_p2_elem_kernel( const HbP2View pv, const HbP2ElemArgs a )
             for ( int d = 0; d < 3; d++ )
                gu[cc][d] = Mi[d] * th[0] + Mi[3 + d] * th[1] + Mi[6 + d] * th[2];
          }
+         double pq = 0.0; // HB_P2_STOKES: - w |det M| p(x_q), added to the diagonal of the stress
+         if ( stokes )
+         {
+            const double s0   = Q[4] * fabs( det );
+            const double divu = gu[0][0] + gu[NC > 1 ? 1 : 0][NC > 1 ? 1 : 0] + gu[NC > 2 ? 2 : 0][NC > 2 ? 2 : 0];
+#pragma unroll
+            for ( int k = 0; k < 4; k++ )
+            {
+               pq -= s0 * pk[k] * lam[k];
+               yp[k] -= s0 * lam[k] * divu;
+            }
+         }
          if ( p1Out )
          {
             // y_i (P1) -= s lambda_i d_c u
@@ -329,7 +344,7 @@ __global__ void hb_p2_elem_kernel( const HbP2View pv, const HbP2ElemArgs a )
             {
 #pragma unroll
                for ( int d = 0; d < 3; d++ )
-                  f[d] = s * ( gu[cc][d] + gu[d < NC ? d : 0][cc] );
+                  f[d] = s * ( gu[cc][d] + gu[d < NC ? d : 0][cc] ) + ( d == cc ? pq : 0.0 );
             }
             else if ( a.form == HB_P2_EPSILON )
             {
@@ -379,6 +394,12 @@ __global__ void hb_p2_elem_kernel( const HbP2View pv, const HbP2ElemArgs a )
                hb_atomic_add( a.accE[c] + eb + ei[k], yv[c][4 + k] );
          }
       }
+      if ( stokes )
+      {
+#pragma unroll
+         for ( int k = 0; k < 4; k++ )
+            hb_atomic_add( a.accP + vb + vi[k], yp[k] );
+      }
    }
 }
 
@@ -388,7 +409,7 @@ void hb_p2_launch_elements( const HbP2View& pv, const HbP2ElemArgs& a, cudaStrea
    const int perCell = ( pv.nAnchors + block - 1 ) / block;
    if ( pv.nCells * perCell <= 0 )
       return;
-   if ( a.form == HB_P2_EPSILON_VECTOR )
+   if ( a.form == HB_P2_EPSILON_VECTOR || a.form == HB_P2_STOKES )
       HB_LAUNCH( hb_p2_elem_kernel< 3 >, pv.nCells * perCell, block, st, pv, a );
    else
       HB_LAUNCH( hb_p2_elem_kernel< 1 >, pv.nCells * perCell, block, st, pv, a );

@@ -16,7 +16,8 @@ enum HbP2Form
    HB_P2_EPSILON  = 1, // int 2 mu eps(phi_j e_d) : eps(phi_i e_c), 4-point degree-2 rule (p2_epsilonvar_blending_q2.cpp)
    HB_P2_DIV      = 2, // P2 -> P1:  - int psi_i d_c phi_j           (p2_to_p1/p2_to_p1_div_blending_q2.cpp, same 4-point rule)
    HB_P2_DIVT     = 3, // P1 -> P2:  - int d_c phi_i psi_j           (p1_to_p2/p1_to_p2_divt_blending_q2.cpp)
-   HB_P2_EPSILON_VECTOR = 4 // all nine epsilon blocks at once on a P2 vector function: y^c_i = int mu ( grad u + grad u^T )_c . grad phi_i
+   HB_P2_EPSILON_VECTOR = 4, // all nine epsilon blocks at once on a P2 vector function: y^c_i = int mu ( grad u + grad u^T )_c . grad phi_i
+   HB_P2_STOKES   = 5  // the whole Taylor-Hood operator in one pass: A u + B^T p ; B u (epsilon A-block, div / divT as above)
 };
 __host__ __device__ __forceinline__ bool hb_p2_form_q2( int form )
 {
@@ -74,6 +75,8 @@ struct HbP2ElemArgs
    const double* srcE[3];
    double*       accV[3]; // zeroed accumulators, same layout as the function; accE null for HB_P2_DIV (P1 destination)
    double*       accE[3];
+   const double* srcP;    // HB_P2_STOKES: pressure (P1) source and accumulator
+   double*       accP;
    const double* kV;   // coefficient as a P2 function (or null)
    const double* kE;
    const double* kq;   // coefficient sampled at the quadrature points [cell][type][anchor][q] (or null; null and no kV: k = 1)

@@ -260,6 +260,13 @@ int hb_p2operator_apply_p1_to_p2( hb_p2operator* op, const hb_function* src, hb_
 hb_p2operator* hb_p2_epsilon_vector_create( hb_storage* st, int min_level, int max_level, const hb_p2function* mu );
 int hb_p2operator_apply_vector( hb_p2operator* op, hb_p2function* const* src3, hb_p2function* const* dst3, int level, int flag, int update_type );
 
+/* The whole P2-P1 Taylor-Hood Stokes operator with the epsilon velocity block in ONE fused kernel: dst.uvw = A src.uvw + B^T src.p,
+ * dst.p = B src.uvw (P2P1ElementwiseBlendingStokesOperator::apply, P2P1ElementwiseBlendingStokesOperator.hpp:91-100, with
+ * P2ElementwiseBlendingEpsilonOperator as A: src/hyteg_operators_composites/stokes/P2P1StokesEpsilonOperator.hpp:50-73); Replace only */
+hb_p2operator* hb_p2_stokes_create( hb_storage* st, int min_level, int max_level, const hb_p2function* mu );
+int hb_p2operator_apply_stokes( hb_p2operator* op, hb_p2function* const* src_uvw, const hb_function* src_p, hb_p2function* const* dst_uvw, hb_function* dst_p,
+                                int level, int flag );
+
 /* Chebyshev-smoothed geometric multigrid on a P2 elementwise operator (BASELINE config 4; the velocity-block recipe of
  * src/terraneo/solvers/StokesMCFGMRESSolver.hpp:71-143): GeometricMultigridSolver + ChebyshevSmoother with the inverse diagonal
  * (radius from power iterations started at eigenvector_guess on max_level, ChebyshevSmoother.hpp:655-665) + quadratic transfer, CG on

@@ -168,7 +168,7 @@ def case_div_blocks(lib, comp):
     assert rc.rel(s.get(w, tol=1e-13)[m], g["shell_L2_divt_%d_inner" % comp][m]) < TOL
 
 
-def case_stokes(lib):
+def case_stokes(lib, fused=True):
     """the fused vector epsilon kernel and the Taylor-Hood composite against the blocks of the oracle (each block pinned to the
     reference: tests/test_p2_oracle_vs_reference.py)"""
     s = P2Setup(lib, "shell", 2)
@@ -181,7 +181,7 @@ def case_stokes(lib):
         v, e = o.to_cells(U[c])
         src.uvw[c].upload(v, e, 2)
     src.p.upload(o.p1.to_cells(pv, 2), 2)
-    S = api.P2P1ElementwiseBlendingEpsilonStokesOperator(s.st, 2, 2, k_xyz)
+    S = api.P2P1ElementwiseBlendingEpsilonStokesOperator(s.st, 2, 2, k_xyz, fused=fused)
     S.apply(src, dst, 2, Inner)
     m = o.mask(Inner)
     B = [o.div_matrix(c) for c in range(3)]

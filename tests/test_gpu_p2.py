@@ -42,8 +42,9 @@ def test_div_blocks(cuda_lib, comp):
     pc.case_div_blocks(cuda_lib, comp)
 
 
-def test_stokes_composite(cuda_lib):
-    pc.case_stokes(cuda_lib)
+@pytest.mark.parametrize("fused", [True, False])
+def test_stokes_composite(cuda_lib, fused):
+    pc.case_stokes(cuda_lib, fused)
 
 
 def test_chebyshev_gmg_matches_reference(cuda_lib):

@@ -37,8 +37,9 @@ def test_div_blocks(emul_lib, comp):
     pc.case_div_blocks(emul_lib, comp)
 
 
-def test_stokes_composite(emul_lib):
-    pc.case_stokes(emul_lib)
+@pytest.mark.parametrize("fused", [True, False])
+def test_stokes_composite(emul_lib, fused):
+    pc.case_stokes(emul_lib, fused)
 
 
 def test_chebyshev_gmg(emul_lib):

@@ -42,7 +42,10 @@ for L in levels:
     ts.p.upload(rng.random(nv), L)
     us_eps = t(lambda: S.A.apply(ts.uvw, td.uvw, L, hb.Inner), reps)
     us_st = t(lambda: S.apply(ts, td, L, hb.Inner), reps)
-    print(json.dumps({"level": L, "epsilon_vector_us": round(us_eps, 1), "stokes_apply_us": round(us_st, 1),
+    fused, S.fused = S.fused, None
+    us_unf = t(lambda: S.apply(ts, td, L, hb.Inner), reps)
+    S.fused = fused
+    print(json.dumps({"level": L, "epsilon_vector_us": round(us_eps, 1), "stokes_apply_us": round(us_st, 1), "stokes_apply_7_kernels_us": round(us_unf, 1),
                       "Gtets_per_s_epsilon": round(n_el / us_eps * 1e-3, 3), "stokes_dofs": 3 * (ndof + nedge) + ndof,
                       "stokes_GDoF_per_s": round((3 * (ndof + nedge) + ndof) / us_st * 1e-3, 3)}), flush=True)
     del A, src, dst, k, st, S, ts, td
