@@ -74,6 +74,7 @@ _SIGNATURES = {
     "hb_p1function_add_scalar": (C.c_int, [_vp, C.c_double, C.c_int, C.c_int]),
     "hb_p1function_mult_elementwise": (C.c_int, [_vp, C.c_int, C.POINTER(_vp), C.c_int, C.c_int]),
     "hb_p1function_dot": (C.c_int, [_vp, _vp, C.c_int, C.c_int, _dp]),
+    "hb_p1function_dot_no_alloc": (C.c_int, [_vp, _vp, C.c_int, C.c_int, _vp]),  # out: DEVICE pointer
     "hb_p1function_sum": (C.c_int, [_vp, C.c_int, C.c_int, _dp]),
     "hb_p1function_max_magnitude": (C.c_int, [_vp, C.c_int, C.c_int, _dp]),
     "hb_p1_constant_laplace_create": (_vp, [_vp, C.c_int, C.c_int]),

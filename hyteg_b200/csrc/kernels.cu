@@ -11,6 +11,8 @@
 #include "kernels.h"
 
 #include "hb_device.h"
+#include <stdexcept>
+#include <string>
 
 #ifdef HB_EMUL
 dim3 threadIdx, blockIdx, blockDim, gridDim;
@@ -1090,6 +1092,59 @@ void hb_launch_reduce( const HbLevelView& lv, const HbBC& bc, int flag, int op, 
    const int block = 256;
 #endif
    const int grid = hb_flat_grid( n, 256, HB_REDUCE_MAX_BLOCKS );
+   HB_LAUNCH( hb_reduce_kernel, grid, block, st, lv, bc, flag, op, a, b, partial );
+   HB_LAUNCH( hb_reduce_final_kernel, 1, block, st, partial, grid, op, out );
+}
+
+// ---------------------------------------------------------------------------------------------
+//  Allocation-free reduction (hb_p1function_dot_no_alloc): the same two kernels as hb_launch_reduce, with the per-CTA partial sums in a
+//  file-scope device array instead of a cudaMalloc'ed buffer.  HB_REDUCE_MAX_BLOCKS doubles (9.25 KB), resident on every GPU that loads the
+//  library until the process exits.  In host code the array's NAME is only a host-side stand-in; the device address comes from
+//  cudaGetSymbolAddress, resolved once per device with that device current and cached.  All calls share the array: nothing in it has to
+//  start at zero (every slot the final pass reads is written by the first pass of the same call), but two calls that overlap on the GPU
+//  (different streams) race on it.
+// ---------------------------------------------------------------------------------------------
+#ifdef HB_EMUL
+static double hb_no_alloc_scratch[HB_REDUCE_MAX_BLOCKS];
+#else
+static __device__ __align__( 256 ) double hb_no_alloc_scratch[HB_REDUCE_MAX_BLOCKS];
+#endif
+
+static double* hb_no_alloc_scratch_address()
+{
+#ifdef HB_EMUL
+   return hb_no_alloc_scratch;
+#else
+   constexpr int  MAXDEV         = 64;
+   static double* cached[MAXDEV] = {};
+   int            dev            = -1;
+   if ( cudaGetDevice( &dev ) != cudaSuccess || dev < 0 || dev >= MAXDEV )
+      throw std::runtime_error( "hyteg_b200: dot_no_alloc: no current CUDA device" );
+   if ( !cached[dev] )
+   {
+      double*           ptr = nullptr;
+      const cudaError_t e   = cudaGetSymbolAddress( (void**) &ptr, hb_no_alloc_scratch );
+      if ( e != cudaSuccess || !ptr )
+         throw std::runtime_error( std::string( "hyteg_b200: dot_no_alloc: cudaGetSymbolAddress failed: " ) + cudaGetErrorString( e ) );
+      cached[dev] = ptr;
+   }
+   return cached[dev];
+#endif
+}
+
+void hb_launch_reduce_no_alloc( const HbLevelView& lv, const HbBC& bc, int flag, int op, const double* a, const double* b, double* out, cudaStream_t st )
+{
+   const size_t n = (size_t) lv.nCells * lv.cellSize;
+   if ( n > (size_t) HB_NO_ALLOC_MAX_ENTRIES )
+      throw std::runtime_error( "hyteg_b200: dot_no_alloc: " + std::to_string( n ) + " entries on this level, the allocation-free path takes at most " +
+                                std::to_string( (long long) HB_NO_ALLOC_MAX_ENTRIES ) + " (HB_NO_ALLOC_MAX_ENTRIES)" );
+#ifdef HB_EMUL
+   const int block = 1;
+#else
+   const int block = 256;
+#endif
+   const int grid = hb_flat_grid( n, 256, HB_REDUCE_MAX_BLOCKS ); // <= the size of the scratch array by construction
+   double*   partial = hb_no_alloc_scratch_address();
    HB_LAUNCH( hb_reduce_kernel, grid, block, st, lv, bc, flag, op, a, b, partial );
    HB_LAUNCH( hb_reduce_final_kernel, 1, block, st, partial, grid, op, out );
 }

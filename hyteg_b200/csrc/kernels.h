@@ -26,6 +26,10 @@ void hb_launch_lincomb( const HbLevelView& lv, const HbLinComb& lc, cudaStream_t
 void hb_launch_multelem( const HbLevelView& lv, const HbLinComb& lc, cudaStream_t st );
 // op 0: sum a*b, 1: sum a, 2: max |a| over owned points selected by flag; result in *out (device)
 void hb_launch_reduce( const HbLevelView& lv, const HbBC& bc, int flag, int op, const double* a, const double* b, double* partial, double* out, cudaStream_t st );
+// the same without any device allocation: partial sums in a file-scope __device__ array (kernels.cu); levels of more than
+// HB_NO_ALLOC_MAX_ENTRIES arena entries are rejected (std::runtime_error)
+#define HB_NO_ALLOC_MAX_ENTRIES ( 1ll << 28 )
+void hb_launch_reduce_no_alloc( const HbLevelView& lv, const HbBC& bc, int flag, int op, const double* a, const double* b, double* out, cudaStream_t st );
 void hb_launch_restrict( const HbLevelView& coarse, const HbLevelView& fine, const double* const* fsrc, double* cdst, const HbBC& bc, int flag, cudaStream_t st );
 void hb_launch_prolongate( const HbLevelView& coarse, const HbLevelView& fine, const double* csrc, double* fdst, const HbBC& bc, int flag, int add, cudaStream_t st );
 // ghost exchange: buf[i] = arena[off[i]] / arena[off[i]] = buf[i]

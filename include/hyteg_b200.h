@@ -145,6 +145,16 @@ int hb_p1function_mult_elementwise( hb_function* dst, int n, hb_function* const*
 /* dotGlobal / sumGlobal / getMaxDoFMagnitude (every DoF counted once; all-reduced when a reducer is set) */
 int hb_p1function_dot( const hb_function* a, const hb_function* b, int level, int flag, double* out );
 int hb_p1function_sum( const hb_function* a, int level, int flag, double* out );
+/* Allocation-free variant of hb_p1function_dot.  No counterpart in the reference: added for callers
+ * that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  The per-CTA partial sums live in a
+ * file-scope __device__ array of the library (1184 doubles = 9.25 KB, held by every GPU that loads the library until exit) instead of
+ * the storage's cudaMalloc'ed buffer; the call allocates nothing, copies nothing to the host and does not synchronise: the result (same
+ * kernels, same summation order, bit-identical to hb_p1function_dot) is written to out_device, ONE double in DEVICE memory supplied by the
+ * caller, in stream order on the stream of hb_set_stream.  Limits: single-rank storages; at most 2^28 arena entries on the level
+ * (n_local_cells * hb_cell_array_size(level)), larger levels are rejected with an error; the level must have been used once before
+ * (its tables are built on first use).  All calls share the scratch array, which keeps the last call's partial sums (no slot needs
+ * clearing: each call overwrites every slot it reads): calls that overlap on the GPU, i.e. on different streams, race. */
+int hb_p1function_dot_no_alloc( const hb_function* a, const hb_function* b, int level, int flag, double* out_device );
 int hb_p1function_max_magnitude( const hb_function* a, int level, int flag, double* out );
 
 /* ---- P1ConstantLaplaceOperator  (src/constant_stencil_operator/P1ConstantOperator.hpp,
