@@ -118,8 +118,16 @@ struct hb_function
    std::vector< hb::DeviceBuffer< double > >  data;    // per level: local arena
    std::vector< hb::DeviceBuffer< double* > > cellPtr; // per level: [nSlots] device pointers
    std::vector< char > mirrorsStale;                   // per level: mirrored cells do not hold the owners' current values
-   void touched( int L ) { mirrorsStale[L - minLevel] = 1; } // call after every write to the level's arena
-   bool stale( int L ) const { return st_nranks() > 1 && mirrorsStale[L - minLevel] != 0; }
+   void touched( int L ) // call after every write to the level's arena
+   {
+      check( L );
+      mirrorsStale[L - minLevel] = 1;
+   }
+   bool stale( int L ) const
+   {
+      check( L );
+      return st_nranks() > 1 && mirrorsStale[L - minLevel] != 0;
+   }
    int  st_nranks() const;
    // arguments for nMessages consecutive ghost exchanges of level L over the peer-memory windows (advances the pair counters);
    // false -- and out.np = 0 -- on one rank or when the windows are not in use

@@ -33,7 +33,8 @@ def run(label, **kv):
     for k in kv: lib.dll.hb_set_tuning(k.encode(), INT_MIN)
 run("interior only", apply_parts=1)
 run("interface only", apply_parts=2)
-run("interface only, descriptor form", apply_parts=2, iface_desc=1)
 run("both, serial", overlap=0)
-run("both, overlapped (default)")
-run("both, overlapped, descriptor form", iface_desc=1)
+run("both, two streams (default)")
+rhs = api.P1Function("r", st, L, L)
+us = t(lambda: A.smooth_jac(dst, rhs, src, 0.66, L, hb.SMOOTH_FLAG))
+print("%s L%d jacobi %8.1f us %6.1f GDoF/s" % (which, L, us, nd / us * 1e-3))
