@@ -426,30 +426,45 @@ __device__ __forceinline__ void hb_p2p_wait_slot( const HbP2PArgs& p, unsigned m
    }
    __syncthreads();
 }
-__device__ __forceinline__ void hb_p2p_put( const double* arena, const long long* __restrict__ sendOff, const HbP2PArgs& p, unsigned m, long long t0, long long stride )
+// A message carries the groups gLo..gHi of every peer's range (HbP2PArgs::sendGrp / recvGrp): element e of peer k's part sits at
+// sendOff[ sendStart[k] + sendGrp[k][gLo] + e ] in the tables and on line e of the pair's window slot.  Pairs with an empty part still
+// count the message (sequence numbers and acks advance for every pair that exchanges anything at all).
+__device__ __forceinline__ void hb_p2p_put( const double* arena, const long long* __restrict__ sendOff, const HbP2PArgs& p, unsigned m, int gLo, int gHi,
+                                            long long t0, long long stride )
 {
-   const long long nS = p.sendStart[p.np];
+   long long cum[HB_P2P_MAXPEERS + 1];
+   cum[0] = 0;
+   for ( int k = 0; k < p.np; k++ )
+      cum[k + 1] = cum[k] + ( p.sendGrp[k][gHi + 1] - p.sendGrp[k][gLo] );
+   const long long nS = cum[p.np];
    for ( long long i = t0; i < nS; i += stride )
    {
       int k = 0;
-      while ( i >= p.sendStart[k + 1] )
+      while ( i >= cum[k + 1] )
          k++;
-      const unsigned long long seq = p.sendSeq[k] + m;
-      HbP2PLine*                   slot = p.remoteData[k] + ( ( seq & 1 ) ? p.segLines : 0 );
-      hb_p2p_store_line( slot + ( i - p.sendStart[k] ), arena[sendOff[i]], (unsigned) seq );
+      const long long          e    = i - cum[k];
+      const unsigned long long seq  = p.sendSeq[k] + m;
+      HbP2PLine*               slot = p.remoteData[k] + ( ( seq & 1 ) ? p.segLines : 0 );
+      hb_p2p_store_line( slot + e, arena[sendOff[p.sendStart[k] + p.sendGrp[k][gLo] + e]], (unsigned) seq );
    }
 }
-__device__ __forceinline__ void hb_p2p_get( double* arena, const long long* __restrict__ recvOff, const HbP2PArgs& p, unsigned m, long long t0, long long stride )
+__device__ __forceinline__ void hb_p2p_get( double* arena, const long long* __restrict__ recvOff, const HbP2PArgs& p, unsigned m, int gLo, int gHi,
+                                            long long t0, long long stride )
 {
-   const long long nR = p.recvStart[p.np];
+   long long cum[HB_P2P_MAXPEERS + 1];
+   cum[0] = 0;
+   for ( int k = 0; k < p.np; k++ )
+      cum[k + 1] = cum[k] + ( p.recvGrp[k][gHi + 1] - p.recvGrp[k][gLo] );
+   const long long nR = cum[p.np];
    for ( long long j = t0; j < nR; j += stride )
    {
       int k = 0;
-      while ( j >= p.recvStart[k + 1] )
+      while ( j >= cum[k + 1] )
          k++;
+      const long long          e    = j - cum[k];
       const unsigned long long seq  = p.recvSeq[k] + m;
-      const HbP2PLine*             slot = p.localData[k] + ( ( seq & 1 ) ? p.segLines : 0 );
-      arena[recvOff[j]]             = hb_p2p_load_line( slot + ( j - p.recvStart[k] ), (unsigned) seq );
+      const HbP2PLine*         slot = p.localData[k] + ( ( seq & 1 ) ? p.segLines : 0 );
+      arena[recvOff[p.recvStart[k] + p.recvGrp[k][gLo] + e]] = hb_p2p_load_line( slot + e, (unsigned) seq );
    }
 }
 // one CTA, after every get of the grid is done: the slot may be overwritten (by message m+2)
@@ -463,13 +478,13 @@ __device__ __forceinline__ void hb_p2p_ack( const HbP2PArgs& p, unsigned m )
 // exchange number m of a launch from INSIDE a kernel whose CTAs can synchronise through bar() (block barrier of a single-CTA
 // kernel, grid barrier of a cooperative launch): everything written to the arena before the call travels
 template < class Bar >
-__device__ __forceinline__ void hb_p2p_exchange_inline( double* arena, const HbP2PArgs& p, unsigned m, Bar bar )
+__device__ __forceinline__ void hb_p2p_exchange_inline( double* arena, const HbP2PArgs& p, unsigned m, int gLo, int gHi, Bar bar )
 {
    const long long t0 = (long long) blockIdx.x * blockDim.x + threadIdx.x, stride = (long long) gridDim.x * blockDim.x;
    bar();
    hb_p2p_wait_slot( p, m );
-   hb_p2p_put( arena, p.sendOff, p, m, t0, stride );
-   hb_p2p_get( arena, p.recvOff, p, m, t0, stride );
+   hb_p2p_put( arena, p.sendOff, p, m, gLo, gHi, t0, stride );
+   hb_p2p_get( arena, p.recvOff, p, m, gLo, gHi, t0, stride );
    bar(); // (no __threadfence() here: it would wait for this thread's NVLink puts to be acknowledged; the barrier orders the arena writes)
    if ( blockIdx.x == 0 )
       hb_p2p_ack( p, m );
@@ -486,8 +501,8 @@ __global__ void __launch_bounds__( 256 ) hb_p2p_exchange_kernel( double* arena, 
    const long long stride = (long long) gridDim.x * blockDim.x;
    const long long t0     = (long long) blockIdx.x * blockDim.x + threadIdx.x;
    hb_p2p_wait_slot( p, 0 );
-   hb_p2p_put( arena, p.sendOff, p, 0, t0, stride );
-   hb_p2p_get( arena, p.recvOff, p, 0, t0, stride );
+   hb_p2p_put( arena, p.sendOff, p, 0, p.gLo, p.gHi, t0, stride );
+   hb_p2p_get( arena, p.recvOff, p, 0, p.gLo, p.gHi, t0, stride );
    __syncthreads();
    if ( threadIdx.x == 0 )
       last = atomicAdd( p.counters, 1u ) == gridDim.x - 1;
@@ -504,7 +519,13 @@ __global__ void __launch_bounds__( 256 ) hb_p2p_exchange_kernel( double* arena, 
 void hb_launch_p2p_exchange( double* arena, const HbP2PArgs& p, cudaStream_t st )
 {
 #ifndef HB_EMUL
-   const long long n    = p.sendStart[p.np] > p.recvStart[p.np] ? p.sendStart[p.np] : p.recvStart[p.np];
+   long long nS = 0, nR = 0;
+   for ( int k = 0; k < p.np; k++ )
+   {
+      nS += p.sendGrp[k][p.gHi + 1] - p.sendGrp[k][p.gLo];
+      nR += p.recvGrp[k][p.gHi + 1] - p.recvGrp[k][p.gLo];
+   }
+   const long long n    = nS > nR ? nS : nR;
    long long       grid = ( n + 1023 ) / 1024; // 4 elements per thread
    if ( grid < 1 )
       grid = 1;
@@ -524,9 +545,9 @@ __global__ void __launch_bounds__( 1024 ) hb_sor_small_kernel( const HbLevelView
    // more than one rank (px.np > 0): the ghost exchanges of the sweep happen in here as well, over the peer-memory windows --
    // after every interface phase but the last one, and (backward sweep) between the interior and the interface phases
    unsigned m        = 0;
-   auto     exchange = [&]() {
+   auto     exchange = [&]( int gLo, int gHi ) { // the point classes written since the last exchange (HB_NGROUP)
       if ( px.np > 0 )
-         hb_p2p_exchange_inline( a.dst, px, m++, [] { __syncthreads(); } );
+         hb_p2p_exchange_inline( a.dst, px, m++, gLo, gHi, [] { __syncthreads(); } );
    };
    const int N = lv.N;
    // the phases walk precomputed work lists (HbLevelView::ifaceItems / phaseItems): no per-phase scan of all interface points
@@ -594,15 +615,16 @@ __global__ void __launch_bounds__( 1024 ) hb_sor_small_kernel( const HbLevelView
    };
    const int nColours[3] = { 1, 2, 3 };
    if ( px.syncFirst )
-      exchange();
+      exchange( px.gLo, px.gHi ); // catch-up: whatever was stale when the sweep started
    if ( !backwards )
    {
       for ( int d = 0; d <= 2; d++ )
          for ( int c = 0; c < nColours[d]; c++ )
          {
             interfacePhase( d, c );
+            const int g = d == 0 ? 0 : ( d == 1 ? 1 + c : 3 + c );
             if ( !( d == 2 && c == 2 ) )
-               exchange();
+               exchange( g, g );
          }
       for ( int c = 0; c < 4; c++ )
          interiorPhase( c );
@@ -611,13 +633,14 @@ __global__ void __launch_bounds__( 1024 ) hb_sor_small_kernel( const HbLevelView
    {
       for ( int c = 3; c >= 0; c-- )
          interiorPhase( c );
-      exchange();
+      exchange( px.gLo, px.gHi ); // the interior class and whatever was stale when the sweep started
       for ( int d = 2; d >= 0; d-- )
          for ( int c = nColours[d] - 1; c >= 0; c-- )
          {
             interfacePhase( d, c );
+            const int g = d == 1 ? 1 + c : 3 + c;
             if ( d != 0 )
-               exchange();
+               exchange( g, g );
          }
    }
 }
@@ -719,7 +742,7 @@ __global__ void __launch_bounds__( HB_BLOCK, 4 )
    {
       interiorColours();
       if ( px.np > 0 )
-         hb_p2p_exchange_inline( a.dst, px, m++, [&] { grid.sync(); } );
+         hb_p2p_exchange_inline( a.dst, px, m++, px.gLo, px.gHi, [&] { grid.sync(); } ); // interior class + what was stale before the sweep
    }
    for ( int ph = 0; ph < 6; ph++ )
    {
@@ -771,7 +794,7 @@ __global__ void __launch_bounds__( HB_BLOCK, 4 )
             hb_commit_block( lv, a, blk );
       }
       if ( px.np > 0 && k != ( backwards ? 0 : 5 ) )
-         hb_p2p_exchange_inline( a.dst, px, m++, [&] { grid.sync(); } ); // starts and ends with a grid barrier
+         hb_p2p_exchange_inline( a.dst, px, m++, k, k, [&] { grid.sync(); } ); // phase k wrote point class k; starts and ends with a grid barrier
       else
          grid.sync();
    }

@@ -43,6 +43,9 @@ struct alignas( 16 ) HbP2PLine
 {
    uint32_t lo, tag0, hi, tag1;
 };
+// exchange groups (classes of travelling points): 0 macro vertices | 1, 2 macro edges by interface colour | 3..5 macro faces by
+// interface colour | 6 macro-cell interiors.  Group k < 6 is exactly what SOR interface phase k writes.
+#define HB_NGROUP 7
 struct HbP2PArgs
 {
    int32_t             np;
@@ -57,6 +60,8 @@ struct HbP2PArgs
    const unsigned long long* localAck[HB_P2P_MAXPEERS];
    unsigned long long  sendSeq[HB_P2P_MAXPEERS], recvSeq[HB_P2P_MAXPEERS]; // 1-based numbers of the launch's first message
    unsigned int*       counters;                                           // [2], zero between launches
+   int32_t             sendGrp[HB_P2P_MAXPEERS][HB_NGROUP + 1], recvGrp[HB_P2P_MAXPEERS][HB_NGROUP + 1]; // group boundaries inside a peer's range
+   int32_t             gLo, gHi; // stand-alone exchange kernel: the groups gLo..gHi travel
 };
 void hb_launch_p2p_exchange( double* arena, const HbP2PArgs& p, cudaStream_t st );
 // whole SOR sweep of a small level in one single-CTA launch; false if the level is too large (or in the emulation build)

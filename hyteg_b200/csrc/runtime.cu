@@ -366,12 +366,26 @@ hb::LevelTables::Exchange& hb_storage::exchange( int L )
       std::sort( l.begin(), l.end() );
       l.erase( std::unique( l.begin(), l.end() ), l.end() );
    }
-   auto offsets = [&]( const std::vector< hb::LocalView::ExchangeEntry >& plan, std::vector< long long >& off, std::vector< long long >& start ) {
+   // class of the travelling point (exchange group, HB_NGROUP): what an SOR phase writes is one group
+   auto groupOf = [&]( int slot, int i ) {
+      const HbBndPoint& p = lt.hXyz[(size_t) i];
+      if ( p.mask == 0 )
+         return HB_NGROUP - 1;
+      const int bits = ( p.mask & 1 ) + ( ( p.mask >> 1 ) & 1 ) + ( ( p.mask >> 2 ) & 1 ) + ( ( p.mask >> 3 ) & 1 );
+      if ( bits >= 3 )
+         return 0;
+      const int colour = hb_interface_colour( view.cells[(size_t) slot], N, p.x, p.y, p.z );
+      return bits == 2 ? 1 + colour : 3 + colour;
+   };
+   auto offsets = [&]( const std::vector< hb::LocalView::ExchangeEntry >& plan, std::vector< long long >& off, std::vector< long long >& start,
+                       std::vector< std::array< int32_t, HB_NGROUP + 1 > >& grp ) {
       off.clear();
       start.assign( ex.peers.size() + 1, 0 );
+      grp.assign( ex.peers.size(), {} );
       for ( size_t k = 0; k < ex.peers.size(); k++ )
       {
          start[k] = (long long) off.size();
+         std::vector< std::pair< int, long long > > el; // (group, arena offset) in (plan entry, local index) order
          for ( const auto& e : plan )
          {
             if ( e.peer != ex.peers[k] )
@@ -383,8 +397,20 @@ hb::LevelTables::Exchange& hb_storage::exchange( int L )
             std::sort( u.begin(), u.end() );
             u.erase( std::unique( u.begin(), u.end() ), u.end() );
             for ( int i : u )
-               off.push_back( (long long) e.slot * lt.view.cellSize + i );
+               el.emplace_back( groupOf( e.slot, i ), (long long) e.slot * lt.view.cellSize + i );
          }
+         // both sides of a pair list the same DoFs in the same order: the plans are in ascending global cell id on both, and the group
+         // of a DoF is a property of the point (the interface colour is canonical), so a stable sort by group keeps them aligned
+         std::stable_sort( el.begin(), el.end(), []( const std::pair< int, long long >& a, const std::pair< int, long long >& b ) { return a.first < b.first; } );
+         int32_t pos = 0;
+         for ( int g = 0; g <= HB_NGROUP; g++ )
+         {
+            while ( pos < (int32_t) el.size() && el[(size_t) pos].first < g )
+               pos++;
+            grp[k][(size_t) g] = g == HB_NGROUP ? (int32_t) el.size() : pos;
+         }
+         for ( const auto& x : el )
+            off.push_back( x.second );
       }
       start[ex.peers.size()] = (long long) off.size();
    };
@@ -396,8 +422,8 @@ hb::LevelTables::Exchange& hb_storage::exchange( int L )
    std::sort( ex.peers.begin(), ex.peers.end() );
    ex.peers.erase( std::unique( ex.peers.begin(), ex.peers.end() ), ex.peers.end() );
    std::vector< long long > so, ro;
-   offsets( view.sendPlan, so, ex.sendStart );
-   offsets( view.recvPlan, ro, ex.recvStart );
+   offsets( view.sendPlan, so, ex.sendStart, ex.sendGrp );
+   offsets( view.recvPlan, ro, ex.recvStart, ex.recvGrp );
    ex.sendOff.upload( so );
    ex.recvOff.upload( ro );
    ex.sendBuf.alloc( so.size() );

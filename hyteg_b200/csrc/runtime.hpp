@@ -1,5 +1,6 @@
 // Host runtime objects behind the C-ABI handles.
 #pragma once
+#include <array>
 #include <map>
 #include <memory>
 #include <stdexcept>
@@ -81,6 +82,11 @@ struct LevelTables
       bool                         built = false;
       std::vector< int >           peers;                // ranks this rank exchanges with (ascending)
       std::vector< long long >     sendStart, recvStart; // [nPeers+1] ranges in sendOff / recvOff
+      // Inside a peer's range the entries are ordered by the CLASS of the travelling point -- group 0: macro vertices, 1-2: macro
+      // edges (interface colour 0, 1), 3-5: macro faces (colour 0..2), 6: macro-cell interiors -- so that an exchange can carry only
+      // the classes written since the last one (an SOR phase writes exactly one).  sendGrp[k][g]: first entry of group g relative
+      // to sendStart[k]; [HB_NGROUP]: the peer's count.
+      std::vector< std::array< int32_t, HB_NGROUP + 1 > > sendGrp, recvGrp;
       DeviceBuffer< long long >    sendOff, recvOff;
       DeviceBuffer< double >       sendBuf, recvBuf;
    } ex;
@@ -117,11 +123,16 @@ struct hb_function
    HbBC        bc;
    std::vector< hb::DeviceBuffer< double > >  data;    // per level: local arena
    std::vector< hb::DeviceBuffer< double* > > cellPtr; // per level: [nSlots] device pointers
-   std::vector< char > mirrorsStale;                   // per level: mirrored cells do not hold the owners' current values
+   std::vector< unsigned char > mirrorsStale;          // per level: bit g set = the mirrored cells do not hold the owners' current
+                                                       // values of point class g (exchange groups, LevelTables::Exchange)
    void touched( int L ) // call after every write to the level's arena
    {
+      touchedGroups( L, ( 1u << HB_NGROUP ) - 1u );
+   }
+   void touchedGroups( int L, unsigned groups ) // ... after a write to points of these classes only (SOR phases)
+   {
       check( L );
-      mirrorsStale[L - minLevel] = 1;
+      mirrorsStale[L - minLevel] |= (unsigned char) groups;
    }
    bool stale( int L ) const
    {

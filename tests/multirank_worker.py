@@ -87,9 +87,16 @@ def main():
         fx, fb, fr = t.fn("x"), t.fn("b"), t.fn("r")
         t.put(fx, x, L)
         t.put(fb, b, L)
+        c0, d0 = comm.exchange_stats(lib)
         for k in range(2):
             t.A.smooth_sor(fx, fb, 1.0, L, pc.SMOOTH)
             t.A.smooth_sor(fx, fb, 1.1, L, pc.SMOOTH, backwards=True)
+        c1, d1 = comm.exchange_stats(lib)
+        if w > 1 and nsend > 0:
+            # an exchange carries only the point classes written since the last one (exchange groups): the 4 sweeps make ~ 24
+            # exchanges but move little more than the whole ghost volume once per sweep, not once per exchange
+            assert c1 - c0 >= 20, (c0, c1)
+            assert d1 - d0 <= 6 * nsend, (d1 - d0, nsend, c1 - c0)
         sor = t.get(fx, L)
         fx.interpolate(lambda X, Y, Z: np.sin(X) * np.sinh(Y) + Z, L, DirichletBoundary)
         fx.interpolate(0.0, L, Inner)
