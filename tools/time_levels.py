@@ -38,3 +38,21 @@ for L in range(1, LMAX + 1):
     tot += lvl
     if rank == 0: print(f"L{L}: sor {sor:8.1f} us  residual {res:7.1f}  restrict {rs:7.1f}  prolongateAndAdd {pr:7.1f}  | V(3,3) share {lvl:8.1f} us")
 if rank == 0: print(f"sum over levels {tot/1e3:.2f} ms (plus CG on level 0)")
+# the coarse-grid solver and the whole cycle as the bench runs it
+cg = api.CGSolver(st, 0, 0, 100, 1e-16, 1e-16)
+b.interpolate(lambda X, Y, Z: X + Y * Z, 0, hb.All)
+def coarse():
+    x.interpolate(0.0, 0, hb.Inner)
+    cg.solve(A, x, b, 0)
+import time
+torch.cuda.synchronize(); t0 = time.perf_counter()
+for _ in range(20): coarse()
+torch.cuda.synchronize()
+if rank == 0: print(f"CG on level 0: {(time.perf_counter() - t0) / 20 * 1e6:.1f} us wall per solve, {cg.iterations()} iterations")
+gmg = api.GeometricMultigridSolver(st, api.GaussSeidelSmoother(st), cg, 0, LMAX, 3, 3)
+b.interpolate(lambda X, Y, Z: X + Y * Z, LMAX, hb.All)
+for _ in range(2): gmg.solve(A, x, b, LMAX)
+torch.cuda.synchronize(); t0 = time.perf_counter()
+for _ in range(10): gmg.solve(A, x, b, LMAX)
+torch.cuda.synchronize()
+if rank == 0: print(f"V(3,3) GS: {(time.perf_counter() - t0) / 10 * 1e3:.3f} ms wall per cycle")
