@@ -9,7 +9,7 @@ OUT = os.path.join(HERE, "libhyteg_b200.so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "--use_fast_math=false",
          "-Xcompiler", "-fPIC", "-shared", "-Xptxas", "-v"]
-SOURCES = ["kernels.cu", "stream_kernel.cu", "shuffle_kernel.cu", "p2_kernels.cu", "runtime.cu", "topology.cpp", "stencil_assembly.cpp", "solvers_capi.cpp"]
+SOURCES = ["kernels.cu", "shuffle_kernel.cu", "p2_kernels.cu", "runtime.cu", "topology.cpp", "stencil_assembly.cpp", "solvers_capi.cpp"]
 
 
 def needs_build():

@@ -50,19 +50,6 @@ struct HbBndChunk
    int32_t first, count, mask, pad;
 };
 
-// Everything block-uniform that the interface kernel needs for one (macro-cell, chunk) block, in one 160-byte record: the
-// block fetches it with a single cooperative load instead of walking chunk -> region -> copy ranges -> copies.
-#define HB_DESC_MAXC 6
-struct HbChunkDesc
-{
-   int32_t      first, count;        // points [first, first+count) of the interface point list
-   uint8_t      mask, bflag, owner, dim;
-   int32_t      nCopies;             // > HB_DESC_MAXC: rc[] is not filled, the kernel walks the tables instead
-   int32_t      gv[4];               // global macro-vertex ids of the cell (interface colouring)
-   HbRegionCopy rc[HB_DESC_MAXC];    // macro-cells containing the primitive, ascending global id
-   int32_t      pad[2];
-};
-
 struct HbCellInfo
 {
    HbRegion region[HB_NMASK];
@@ -140,7 +127,7 @@ struct HbLevelView
    const HbBndChunk*   chunks; // [nChunks] interface points grouped by region (identical for every macro-cell)
    int32_t             nChunks;
    int32_t             pad0;
-   const HbChunkDesc*  descs; // [nCells * nChunks] or null
+   const void*         reserved0;
    const HbIfaceItem*  ifaceItems;
    int32_t             ifaceStart[7]; // phase k: [ifaceStart[k], ifaceStart[k+1]); ifaceFaces = 0: phases 3..5 are not listed
    int32_t             ifaceFaces;

@@ -179,133 +179,6 @@ __device__ __forceinline__ void hb_boundary_block( const HbLevelView& lv, const 
    }
 }
 
-#ifndef HB_EMUL
-// Same block, descriptor form (sm_100a path): the block-uniform data -- chunk, region flags, the macro-cells containing the
-// primitive with their coordinate maps, and their weights -- are fetched cooperatively into shared memory in two steps, so a
-// thread's dependent chain is  descriptor -> point coordinates + weights -> neighbour values  instead of six table look-ups.
-// For the common two-copy case (macro faces) the neighbour loads of both macro-cells are issued before the first FMA.
-// Arithmetic and summation order are those of hb_boundary_stencil (bit-identical results).
-template < int MODE >
-__device__ __forceinline__ void hb_boundary_block_desc( const HbLevelView& lv, const HbStencilArgs& a, int blk )
-{
-   __shared__ HbChunkDesc sd;
-   __shared__ double      sW[HB_DESC_MAXC][16];
-   const int cell = blk / lv.nChunks;
-   if ( cell >= lv.nCells )
-      return;
-   __syncthreads(); // previous block of a persistent CTA is done with sd / sW
-   if ( threadIdx.x < sizeof( HbChunkDesc ) / 4 )
-      ( (int32_t*) &sd )[threadIdx.x] = ( (const int32_t*) ( lv.descs + blk ) )[threadIdx.x];
-   __syncthreads();
-   if ( !( sd.owner & 2 ) || !( ( a.selMask >> sd.bflag ) & 1 ) || !( ( a.dimSel >> sd.dim ) & 1 ) )
-      return; // block-uniform
-   if ( ( ( a.dimSel & 16 ) && ( sd.owner & 4 ) ) || ( ( a.dimSel & 32 ) && !( sd.owner & 4 ) ) )
-      return;
-   const int nC = sd.nCopies;
-   if ( nC > HB_DESC_MAXC )
-   {
-      hb_boundary_block< MODE >( lv, a, blk ); // macro edges / vertices shared by many macro-cells: table walk
-      return;
-   }
-   const int N = lv.N;
-   if ( (int) threadIdx.x < nC * HB_NDIR )
-   {
-      const int e = threadIdx.x / HB_NDIR, d = threadIdx.x - e * HB_NDIR;
-      sW[e][d]    = a.W[( (size_t) sd.rc[e].slot * HB_NMASK + sd.rc[e].maskp ) * HB_NDIR + d];
-   }
-   const bool       active = (int) threadIdx.x < sd.count;
-   const int        i      = sd.first + ( active ? threadIdx.x : 0 );
-   const HbBndPoint p      = lv.bnd[i];
-   __syncthreads();
-   if ( !active )
-      return;
-   if ( a.bndColour >= 0 )
-   {
-      if ( hb_interface_colour_gv( sd.gv, N, p.x, p.y, p.z ) != a.bndColour )
-         return;
-   }
-   const int x = p.x, y = p.y, z = p.z;
-   // neighbour values of copy e (0 for directions that leave the macro-cell), all loads issued together
-   auto gather = [&]( int e, double ( &v )[HB_NDIR] ) {
-      const HbRegionCopy& rc = sd.rc[e];
-      const int           xp = rc.c[0][0] * N + rc.c[0][1] * x + rc.c[0][2] * y + rc.c[0][3] * z;
-      const int           yp = rc.c[1][0] * N + rc.c[1][1] * x + rc.c[1][2] * y + rc.c[1][3] * z;
-      const int           zp = rc.c[2][0] * N + rc.c[2][1] * x + rc.c[2][2] * y + rc.c[2][3] * z;
-      const double* __restrict__ s = rc.slot < lv.nCells ? a.srcBase + (size_t) rc.slot * lv.cellSize : a.src[rc.slot];
-      const int vm   = hb_valid[rc.maskp];
-      const int ws   = N + 1 - zp;
-      const int i0   = hb_index( N, xp, yp, zp );
-      const int szUp = ( ws * ( ws + 1 ) ) / 2, szDn = ( ( ws + 1 ) * ( ws + 2 ) ) / 2;
-      const int dN = ws - yp, dS = -( ws - yp + 1 ), dT = szUp - yp, dTS = szUp - ws, dB = yp - szDn, dBN = ws + 1 - szDn;
-      int       idx[HB_NDIR];
-      idx[D_C]   = i0;
-      idx[D_W]   = i0 - 1;
-      idx[D_E]   = i0 + 1;
-      idx[D_N]   = i0 + dN;
-      idx[D_S]   = i0 + dS;
-      idx[D_NW]  = i0 + dN - 1;
-      idx[D_SE]  = i0 + dS + 1;
-      idx[D_TC]  = i0 + dT;
-      idx[D_TW]  = i0 + dT - 1;
-      idx[D_TS]  = i0 + dTS;
-      idx[D_TSE] = i0 + dTS + 1;
-      idx[D_BC]  = i0 + dB;
-      idx[D_BN]  = i0 + dBN;
-      idx[D_BE]  = i0 + dB + 1;
-      idx[D_BNW] = i0 + dBN - 1;
-#pragma unroll
-      for ( int d = 1; d < HB_NDIR; d++ )
-         v[d] = ( ( vm >> d ) & 1 ) ? s[idx[d]] : 0.0;
-   };
-   auto partial = [&]( int e, const double ( &v )[HB_NDIR] ) {
-      double part = 0.0;
-#pragma unroll
-      for ( int d = 1; d < HB_NDIR; d++ )
-         part += sW[e][d] * v[d];
-      return part;
-   };
-   double sNb = 0.0, diag = 0.0;
-   if ( nC == 2 )
-   {
-      double v0[HB_NDIR], v1[HB_NDIR];
-      gather( 0, v0 );
-      gather( 1, v1 );
-      sNb += partial( 0, v0 );
-      diag += sW[0][0];
-      sNb += partial( 1, v1 );
-      diag += sW[1][0];
-   }
-   else
-      for ( int e = 0; e < nC; e++ )
-      {
-         double v[HB_NDIR];
-         gather( e, v );
-         sNb += partial( e, v );
-         diag += sW[e][0];
-      }
-   const size_t gi     = (size_t) cell * lv.cellSize + (size_t) hb_index( N, x, y, z );
-   const double centre = a.srcBase[gi];
-   double       val;
-   hb_epilogue< MODE >( a, &val, gi, sNb, diag, centre ); // CHEB_STEP also updates aux[gi]
-   if ( a.toScratch )
-   {
-      a.scratch[(size_t) cell * lv.nBnd + i] = val;
-      return;
-   }
-   const double auxVal = ( MODE == HB_CHEB_STEP ) ? a.aux[gi] : 0.0;
-   for ( int e = 0; e < nC; e++ )
-   {
-      const HbRegionCopy& rc = sd.rc[e];
-      if ( rc.slot >= lv.nCells )
-         continue;
-      const size_t gj = (size_t) rc.slot * lv.cellSize + (size_t) hb_copy_index( N, rc, x, y, z );
-      a.dst[gj]       = val;
-      if ( MODE == HB_CHEB_STEP )
-         a.aux[gj] = auxVal;
-   }
-}
-#endif
-
 // grid = nInteriorBlocks + nBoundaryBlocks.  Interior block b -> (cell, tile); its 8 warps take 8
 // consecutive z-slices of the same (y,x) tile so that the slices shared between neighbouring warps
 // are served by L1 instead of L2.
@@ -331,15 +204,6 @@ __global__ void __launch_bounds__( HB_BLOCK, 4 ) hb_interface_kernel( const HbLe
 {
    hb_boundary_block< MODE >( lv, a, blockIdx.x );
 }
-
-#ifndef HB_EMUL
-// descriptor form (see hb_boundary_block_desc): 3 CTAs/SM, both macro-cells' neighbour loads in flight at once
-template < int MODE >
-__global__ void __launch_bounds__( HB_BLOCK, 3 ) hb_interface_desc_kernel( const HbLevelView lv, const HbStencilArgs a )
-{
-   hb_boundary_block_desc< MODE >( lv, a, blockIdx.x );
-}
-#endif
 
 // scratch -> all local copies, for the interface phases of SOR
 __global__ void hb_commit_kernel( const HbLevelView lv, const HbStencilArgs a )
@@ -868,10 +732,6 @@ bool hb_launch_sor_small( const HbLevelView& lv, const HbStencilArgs& a, int bac
 #endif
 }
 
-// Interface kernel in descriptor form: A/B knob "iface_desc".  Measured on B200 (level 8, cube_6el): 25.0 us vs 24.9 us for the
-// table walk -- the kernel is bound by the L1 wavefronts of its scattered gathers, not by its dependent look-ups -- so the
-// table walk (4 CTAs/SM) stays the default.
-int hb_use_desc = 0;
 int hb_coop_ctas_per_sm = 0; // A/B knob "sor_coop_ctas": CTAs per SM of the cooperative SOR launch (0: as many as fit)
 
 template < int MODE >
@@ -884,13 +744,6 @@ static void hb_launch_stencil_mode( const HbLevelView& lv, const HbStencilArgs& 
       return;
    if ( nIntBlocks == 0 )
    {
-#ifndef HB_EMUL
-      if ( lv.descs && hb_use_desc )
-      {
-         hb_interface_desc_kernel< MODE ><<< (unsigned) grid, HB_BLOCK, 0, st >>>( lv, a );
-         return;
-      }
-#endif
       HB_LAUNCH( hb_interface_kernel< MODE >, (unsigned) grid, HB_BLOCK, st, lv, a );
       return;
    }

@@ -74,4 +74,3 @@ bool hb_sor_coop_available();
 // interior != 0 (needs HbLevelView::phaseItems): the four interior colours run in the same launch -- the whole sweep
 bool hb_launch_sor_interface_coop( const HbLevelView& lv, const HbStencilArgs& a, int backwards, int kLo, int kHi, const HbP2PArgs& px, int interior, cudaStream_t st );
 extern int hb_coop_ctas_per_sm; // cooperative SOR launch: CTAs per SM (0: as many as fit)
-extern int hb_use_desc; // 1: interface kernel reads per-block descriptors, 0: walks the topology tables (default)

@@ -87,7 +87,6 @@ void hb_storage::uploadTopologyTables()
    dRegionCopies.upload( view.regionCopies );
    for ( auto& kv : levels )
    {
-      buildChunkDescs( *kv.second );
       buildPhaseItems( *kv.second );
       kv.second->view.cells  = dCells.ptr;
       kv.second->view.copies = dCopies.ptr;
@@ -96,34 +95,6 @@ void hb_storage::uploadTopologyTables()
    }
    tablesDirty = false;
    g_constOwner = nullptr; // macro-cell flags may have changed (operators created afterwards stage the new flags)
-}
-
-void hb_storage::buildChunkDescs( hb::LevelTables& lt )
-{
-   static_assert( sizeof( HbChunkDesc ) == 160, "HbChunkDesc layout" );
-   std::vector< HbChunkDesc > d( (size_t) view.nLocal * lt.hChunks.size() );
-   for ( int c = 0; c < view.nLocal; c++ )
-      for ( size_t k = 0; k < lt.hChunks.size(); k++ )
-      {
-         const HbBndChunk& ch = lt.hChunks[k];
-         const HbCellInfo& ci = view.cells[c];
-         HbChunkDesc&      o  = d[(size_t) c * lt.hChunks.size() + k];
-         std::memset( &o, 0, sizeof( o ) );
-         o.first   = ch.first;
-         o.count   = ch.count;
-         o.mask    = (uint8_t) ch.mask;
-         o.bflag   = ci.region[ch.mask].bflag;
-         o.owner   = ci.region[ch.mask].owner;
-         o.dim     = ci.region[ch.mask].dim;
-         o.nCopies = ci.rcBegin[ch.mask + 1] - ci.rcBegin[ch.mask];
-         for ( int j = 0; j < 4; j++ )
-            o.gv[j] = ci.gv[j];
-         if ( o.nCopies <= HB_DESC_MAXC )
-            for ( int e = 0; e < o.nCopies; e++ )
-               o.rc[e] = view.regionCopies[ci.rcBegin[ch.mask] + e];
-      }
-   lt.descs.upload( d );
-   lt.view.descs = lt.descs.ptr;
 }
 
 void hb_storage::buildPhaseItems( hb::LevelTables& lt )
@@ -308,8 +279,6 @@ hb::LevelTables& hb_storage::level( int L )
    lt->tiles.upload( tiles );
    {
       std::vector< HbItem > items;
-      hb_stream_build_items( N, items );
-      lt->items.upload( items );
       hb_shuffle_build_items( N, items, hb::tuning( "shuffle_ys", 0 ), hb::tuning( "shuffle_order", 0 ) );
       lt->itemsShuffle.upload( items );
    }
@@ -332,7 +301,6 @@ hb::LevelTables& hb_storage::level( int L )
    v.regionCopies = dRegionCopies.ptr;
    v.chunks       = lt->chunks.ptr;
    v.nChunks      = (int) chunks.size();
-   buildChunkDescs( *lt );
    buildPhaseItems( *lt );
    auto& ref      = *lt;
    levels[L]      = std::move( lt );
@@ -484,8 +452,6 @@ int hb_set_allreduce( hb_allreduce_fn fn, void* ctx )
 
 int hb_set_tuning( const char* key, int value )
 {
-   if ( std::string( key ) == "iface_desc" )
-      hb_use_desc = ( value == -2147483647 - 1 ) ? 0 : value;
    if ( std::string( key ) == "sor_coop_ctas" )
       hb_coop_ctas_per_sm = ( value == -2147483647 - 1 ) ? 0 : value;
    if ( value == -2147483647 - 1 ) // INT_MIN: back to the built-in default
@@ -517,8 +483,6 @@ hb_storage* hb_storage_create_partitioned( int nV, const double* xyz, int nC, co
    st->view.nRanks = nRanks;
    st->reducePartial.alloc( HB_REDUCE_MAX_BLOCKS );
    st->reduceOut.alloc( 8 );
-   st->workCounter.alloc( 2 );
-   cudaCheck( cudaMemset( st->workCounter.ptr, 0, 2 * sizeof( int32_t ) ), "cudaMemset" );
    cudaCheck( cudaMallocHost( (void**) &st->hReduce, 8 * sizeof( double ) ), "cudaMallocHost" );
    st->uploadTopologyTables();
    return st.release();

@@ -69,8 +69,6 @@ struct LevelTables
    std::vector< HbBndPoint >  hBnd;
    DeviceBuffer< HbIfaceItem > ifaceItems; // work lists of the cooperative SOR interface launch
    DeviceBuffer< HbPhaseItem > phaseItems; // work lists of the single-CTA SOR sweep, rebuilt with the topology tables
-   DeviceBuffer< HbChunkDesc > descs; // per (local macro-cell, chunk), rebuilt with the topology tables
-   DeviceBuffer< HbItem >     items;   // work items of the TMA-streamed interior kernel
    DeviceBuffer< HbItem >     itemsShuffle; // work items of the centre-column + shuffle interior kernel
    DeviceBuffer< double >     scratch; // nCells*nBnd, interface staging (SOR)
    std::vector< HbBndPoint >  hXyz;    // host copy of the coordinate template
@@ -104,13 +102,11 @@ struct hb_storage
    std::map< int, std::unique_ptr< hb::LevelTables > > levels;
    hb::DeviceBuffer< double >               reducePartial; // HB_REDUCE_MAX_BLOCKS
    hb::DeviceBuffer< double >               reduceOut;     // 8 slots
-   hb::DeviceBuffer< int32_t >              workCounter;   // [2] streamed-kernel work counters (zero between launches)
    double*                                  hReduce = nullptr; // pinned
    bool                                     tablesDirty = true;
 
    hb::LevelTables& level( int L );
    hb::LevelTables::Exchange& exchange( int L );
-   void             buildChunkDescs( hb::LevelTables& lt ); // builds the level's exchange tables on first use
    void             buildPhaseItems( hb::LevelTables& lt );
    void             uploadTopologyTables();
    ~hb_storage();

@@ -86,14 +86,14 @@ __device__ __forceinline__ double epilogue( const HbStencilArgs& a, double Ax, d
 
 namespace {
 
-template < int MODE, int DEPTH, int REGS = 128 >
-__global__ void __maxnreg__( REGS ) hb_shuffle_kernel( const HbLevelView lv, const HbStencilArgs a, const HbStreamArgs sa )
+template < int MODE, int DEPTH >
+__global__ void __maxnreg__( 128 ) hb_shuffle_kernel( const HbLevelView lv, const HbStencilArgs a, const HbStreamArgs sa )
 {
    constexpr bool EX = ModeTraits< MODE >::hasExtra;
    const int      N  = lv.N;
    // item-major order: CTAs of consecutive block ids work on the same item of different macro-cells
    int       itemIdx, cell;
-   const int nc = sa.cellCount ? sa.cellCount : lv.nCells;
+   const int nc = lv.nCells;
    if ( sa.cellMajor )
    {
       cell    = blockIdx.x / sa.nItems;
@@ -104,7 +104,6 @@ __global__ void __maxnreg__( REGS ) hb_shuffle_kernel( const HbLevelView lv, con
       itemIdx = blockIdx.x / nc;
       cell    = blockIdx.x - itemIdx * nc;
    }
-   cell += sa.cellFirst;
    if ( !( ( sa.selMask >> c_bflag[sa.constBase + cell] ) & 1 ) )
       return;
    const HbItem it   = sa.items[itemIdx];
@@ -128,10 +127,8 @@ __global__ void __maxnreg__( REGS ) hb_shuffle_kernel( const HbLevelView lv, con
    // independent of each other.  Addresses are opaque 64-bit integers and the accesses are PTX, so the compiler neither
    // re-derives them from indices nor serialises them.
    using u64       = unsigned long long;
-   // sa.sync bits 1,2,3 are measurement probes (tools/sweep_order.py): all cells read macro-cell 0 / nothing is stored / all
-   // cells store into macro-cell 0
-   const u64 srcB  = (u64) ( sa.srcArena + ( ( sa.sync & 2 ) ? 0 : cellBase ) );
-   const u64 dstB  = (u64) ( a.dst + ( ( sa.sync & 8 ) ? 0 : cellBase ) ); // probe 8: all cells store into macro-cell 0
+   const u64 srcB  = (u64) ( sa.srcArena + cellBase );
+   const u64 dstB  = (u64) ( a.dst + cellBase );
    const u64 exB   = EX ? (u64) ( sa.extraArena + cellBase ) : 0ull;
    const int ya    = it.ya, nOut = it.nOut; // CTA-uniform trip count: keeps the shuffles in provably convergent code
    const int rowIn = row_base( N, ya - 1, zA - 1 ) + xc; // slice zA-1, row ya-1
@@ -154,7 +151,7 @@ __global__ void __maxnreg__( REGS ) hb_shuffle_kernel( const HbLevelView lv, con
    const bool laneOut = CHAIN2 ? ( lane >= 2 ) : ( ( lane >= 1 ) && ( lane <= XOUT ) );
    const int  yMax0   = laneOut ? min( ya + nOut - 1, min( N - 2 - zA, N - 1 - zA - xo ) ) : -1;
    const int  yMax1   = ( laneOut && zA + 1 <= N - 3 ) ? min( ya + nOut - 1, min( N - 3 - zA, N - 2 - zA - xo ) ) : -1;
-   int        r0 = ( sa.sync & 4 ) ? 0 : max( 0, yMax0 - ya + 1 ), r1 = ( sa.sync & 4 ) ? 0 : max( 0, yMax1 - ya + 1 ); // rows this lane still has to store in slice zA / zA+1
+   int        r0 = max( 0, yMax0 - ya + 1 ), r1 = max( 0, yMax1 - ya + 1 ); // rows this lane still has to store in slice zA / zA+1
    // SOR: colour (x + 2y + 3z) mod 4 of the output point (same colouring as the generic kernel); k0 == 0 mod 4 <=> slice zA matches
    int k0 = ( MODE == HB_SOR ) ? ( xc + 2 * ya + 3 * zA - a.colour ) : 0;
 
@@ -353,12 +350,9 @@ __global__ void __maxnreg__( REGS ) hb_shuffle_kernel( const HbLevelView lv, con
          k0 += 2 * DEPTH;
    };
    int left = nOut; // output rows still to produce
-   // optional CTA-wide pacing: the warps of a CTA share input slices pairwise, keeping them on the same rows keeps those in L1
-   const int nSync = ( ( sa.sync & 1 ) && XCH == 1 ) ? 32 * min( PAIRS, ( N - 3 - it.z0 ) / 2 + 1 ) : 0;
    while ( nLoad >= DEPTH )
    {
-      if ( nSync )
-         asm volatile( "bar.sync 1, %0;" ::"r"( nSync ) : "memory" );
+      asm volatile( "" ::: "memory" ); // keeps the unrolled blocks apart: without it ptxas schedules the fused modes 7 % longer
       block( std::false_type{} );
       left -= DEPTH;
    }
@@ -396,26 +390,9 @@ bool hb_shuffle_supported( int mode, const HbLevelView& lv )
           mode == HB_CHEB_STEP || mode == HB_SOR;
 }
 
-// experimental register budgets (more resident CTAs per SM): apply and Jacobi only
-template < int DEPTH, int REGS >
-static bool launchRegs( int mode, unsigned g, unsigned b, const HbLevelView& lv, const HbStencilArgs& a, const HbStreamArgs& sa, cudaStream_t st )
-{
-   if ( mode == HB_APPLY_REPLACE )
-      hb_shuffle_kernel< HB_APPLY_REPLACE, DEPTH, REGS ><<< g, b, 0, st >>>( lv, a, sa );
-   else if ( mode == HB_JACOBI )
-      hb_shuffle_kernel< HB_JACOBI, DEPTH, REGS ><<< g, b, 0, st >>>( lv, a, sa );
-   else
-      return false;
-   return true;
-}
-
 template < int DEPTH >
-static void launchDepth( int mode, unsigned g, unsigned b, const HbLevelView& lv, const HbStencilArgs& a, const HbStreamArgs& sa, cudaStream_t st, int regs = 0 )
+static void launchDepth( int mode, unsigned g, unsigned b, const HbLevelView& lv, const HbStencilArgs& a, const HbStreamArgs& sa, cudaStream_t st )
 {
-   if ( DEPTH <= 5 && regs == 1 && launchRegs< ( DEPTH <= 5 ? DEPTH : 3 ), 96 >( mode, g, b, lv, a, sa, st ) )
-      return;
-   if ( DEPTH <= 5 && regs == 2 && launchRegs< ( DEPTH <= 5 ? DEPTH : 3 ), 80 >( mode, g, b, lv, a, sa, st ) )
-      return;
    switch ( mode )
    {
    case HB_APPLY_REPLACE:
@@ -446,27 +423,25 @@ static void launchDepth( int mode, unsigned g, unsigned b, const HbLevelView& lv
 
 void hb_launch_shuffle_stencil( int mode, const HbLevelView& lv, const HbStencilArgs& a, const HbStreamArgs& sa, cudaStream_t st, int depth )
 {
-   const long long grid = (long long) ( sa.cellCount ? sa.cellCount : lv.nCells ) * sa.nItems;
+   const long long grid = (long long) lv.nCells * sa.nItems;
    if ( grid < 1 )
       return;
    const unsigned g = (unsigned) grid, b = PAIRS * 32;
-   const int regs = depth / 100; // tuning: 100 * register-budget code + depth
-   depth %= 100;
    if ( depth <= 0 ) // measured best on B200 with 4-warp CTAs (profiles/r1_b_interior_sweeps.txt)
       depth = 4;
    switch ( depth )
    {
    case 3:
-      launchDepth< 3 >( mode, g, b, lv, a, sa, st, regs );
+      launchDepth< 3 >( mode, g, b, lv, a, sa, st );
       break;
    case 4:
-      launchDepth< 4 >( mode, g, b, lv, a, sa, st, regs );
+      launchDepth< 4 >( mode, g, b, lv, a, sa, st );
       break;
    case 7:
       launchDepth< 7 >( mode, g, b, lv, a, sa, st );
       break;
    default:
-      launchDepth< DEPTH_DEFAULT >( mode, g, b, lv, a, sa, st, regs );
+      launchDepth< DEPTH_DEFAULT >( mode, g, b, lv, a, sa, st );
    }
 }
 

@@ -11,8 +11,6 @@ lib = hb.get_lib(); lib.check(lib.dll.hb_device_init(0))
 s = torch.cuda.current_stream(); lib.dll.hb_set_stream(s.cuda_stream)
 v, c = meshes.cube_6el() if which == "cube" else meshes.spherical_shell(2, 2, 0.5, 1.0)
 INT_MIN = -2147483648
-if os.environ.get("LOWPRIO"):
-    lib.dll.hb_set_tuning(b"overlap_low_priority", 1)  # read once, when the side stream is created
 def t(fn, n=20):
     for _ in range(3): fn()
     torch.cuda.synchronize()

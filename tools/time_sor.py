@@ -31,7 +31,5 @@ run("default (four colours, coop six phases, direct)")
 run("stage all", sor_stage_all=1)
 run("coop small only (r1 phases)", sor_coop=2)
 run("no coop", sor_coop=0)
-for cw in (1, 2, 3):
-    run("cellwise %d" % cw, sor_cellwise=cw)
 run("depth 3", shuffle_depth=3)
 run("depth 5", shuffle_depth=5)
