@@ -124,7 +124,7 @@ def workload_name(level, gpus, mesh="auto"):
     if kind == "cubes":
         return f"box of {gpus} cubes (6 macro-tets each) level {level} P1 Laplace constant-stencil apply, one cube per GPU"
     return (f"spherical shell meshSphericalShell(2,{gpus + 1},0.5,1.0) ({60 * gpus} macro-tets) level {level} P1 Laplace constant-stencil apply, "
-            f"macro-cells partitioned into {gpus} connected blocks of 60 (greedy balancer)")
+            f"one radial layer of 60 macro-tets per GPU")
 
 
 def host_cores():
@@ -238,15 +238,15 @@ def main():
         k, val = kv.split("=")
         lib.dll.hb_set_tuning(k.encode(), int(val))
     from hyteg_b200 import comm
-    # weak scaling (BASELINE configs[4]): the spherical shell with one radial layer of 60 macro-tets per GPU, partitioned into connected
-    # blocks by the greedy balancer (every rank has several neighbour ranks); the ghost layers travel over NVLink inside the step:
+    # weak scaling (BASELINE configs[4]): the spherical shell with one radial layer of 60 macro-tets per GPU (a rank's neighbours are the
+    # layers below and above it: two whole spherical surfaces of ghost data); the ghost layers travel over NVLink inside the step:
     # remote stores into the neighbours' peer-memory windows (HB_P2P=0: pack -> ncclSend/ncclRecv -> unpack)
     (v, c), mesh_kind = workload_mesh(world, args.mesh)
     cell_rank = None
     if world > 1:
         comm.init_nccl(lib, segment_bytes=256 << 20)  # the shell's interfaces are whole spherical surfaces: several million doubles per pair at level 8
         if mesh_kind == "shell":
-            cell_rank = meshes.partition_greedy(c, world)
+            cell_rank = meshes.partition_radial_layers(v, c, world)
     st = api.PrimitiveStorage(v, c, rank, world, cell_rank=cell_rank)
     st.setMeshBoundaryFlagsOnBoundary(1, 0, True)
     A = api.P1ConstantLaplaceOperator(st, 0, L)

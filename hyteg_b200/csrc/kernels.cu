@@ -380,6 +380,7 @@ __global__ void __launch_bounds__( 256 ) hb_p2p_exchange_kernel( double* arena, 
 }
 #endif
 
+int hb_p2p_grid_waves = 0; // tuning "p2p_grid_waves": CTAs of the stand-alone exchange kernel, in units of 148 (0: default)
 void hb_launch_p2p_exchange( double* arena, const HbP2PArgs& p, cudaStream_t st )
 {
 #ifndef HB_EMUL
@@ -393,8 +394,11 @@ void hb_launch_p2p_exchange( double* arena, const HbP2PArgs& p, cudaStream_t st 
    long long       grid = ( n + 1023 ) / 1024; // 4 elements per thread
    if ( grid < 1 )
       grid = 1;
-   if ( grid > 148 )
-      grid = 148;
+   // every element is a chain of dependent accesses (offset -> value -> remote store; poll -> offset -> store): what moves the data
+   // is the number of threads in flight, and no CTA waits for another one of its grid, so the grid may exceed one wave
+   const long long cap = 148ll * ( hb_p2p_grid_waves > 0 ? hb_p2p_grid_waves : 8 );
+   if ( grid > cap )
+      grid = cap;
    hb_p2p_exchange_kernel<<< (unsigned) grid, 256, 0, st >>>( arena, p );
 #endif
 }

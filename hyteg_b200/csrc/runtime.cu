@@ -452,6 +452,8 @@ int hb_set_allreduce( hb_allreduce_fn fn, void* ctx )
 
 int hb_set_tuning( const char* key, int value )
 {
+   if ( std::string( key ) == "p2p_grid_waves" )
+      hb_p2p_grid_waves = ( value == -2147483647 - 1 ) ? 0 : value;
    if ( std::string( key ) == "sor_coop_ctas" )
       hb_coop_ctas_per_sm = ( value == -2147483647 - 1 ) ? 0 : value;
    if ( value == -2147483647 - 1 ) // INT_MIN: back to the built-in default

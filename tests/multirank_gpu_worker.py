@@ -29,6 +29,9 @@ def main():
     lib = hb.get_lib()
     lib.check(lib.dll.hb_device_init(local))
     comm.init_nccl(lib)
+    for kv in filter(None, os.environ.get("HB_TUNING", "").split(",")):  # e.g. exchange_groups=0
+        k, val = kv.split("=")
+        lib.dll.hb_set_tuning(k.encode(), int(val))
     mesh = meshes.cuboid(world, 1, 1, hi=(float(world), 1.0, 1.0))
     own = lambda a: ~np.isnan(a)
 
