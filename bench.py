@@ -45,6 +45,8 @@ def parse():
     p.add_argument("--impl", default="ours")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--mesh", default="auto", choices=["auto", "shell", "cubes"], help="auto: cube_6el on one GPU, the spherical shell on several")
+    p.add_argument("--replicate-below", type=int, default=4,
+                   help="more than one GPU: multigrid levels 0 .. this one run on a replica of the whole mesh on every rank (-1: all levels distributed)")
     p.add_argument("--p2-level", type=int, default=6, help="BASELINE config 3 (P2 div-k-grad with blending on the shell) level; 0: skip")
     return p.parse_args()
 
@@ -307,10 +309,20 @@ def main():
     # V(3,3) cycle, Gauss-Seidel smoother, CG on level 0
     x, b = api.P1Function("x", st, 0, L), api.P1Function("b", st, 0, L)
     x.interpolate(1.0, L, hb.DirichletBoundary)
-    gmg = api.GeometricMultigridSolver(st, api.GaussSeidelSmoother(st), api.CGSolver(st, 0, 0, 50, 1e-16, 1e-16), 0, L, 3, 3)
+    # more than one rank: the levels 0 .. LREP of the cycle run on a replica of the whole mesh, redundantly on every rank -- the same
+    # operations without their ghost exchanges (~ 40 per level and cycle, three all-reduces per CG iteration); knob --replicate-below
+    LREP = min(args.replicate_below, L - 1) if world > 1 else -1
+    if LREP >= 0:
+        # level 0 (12 (gpus + 1) macro vertices) by dense Cholesky on the host instead of <= 50 CG iterations with three host-read dot
+        # products each (cg_max_iter = 0; the reference's counterpart as coarse-grid solver is PETScLUSolver)
+        coarse_gs = api.ReplicatedCoarseCycle(st, LREP, "gs", 0.66, 3, 3, 0)
+        coarse_j = api.ReplicatedCoarseCycle(st, LREP, "jacobi", 0.66, 3, 3, 0)
+    else:
+        coarse_gs = coarse_j = None
+    gmg = api.GeometricMultigridSolver(st, api.GaussSeidelSmoother(st), coarse_gs or api.CGSolver(st, 0, 0, 50, 1e-16, 1e-16), max(LREP, 0), L, 3, 3)
     ms_v = timed(lambda: gmg.solve(A, x, b, L), max(args.steps // 10, 2), 2)
     # same cycle with the fused weighted-Jacobi sweep as smoother (one kernel pair per sweep instead of ten SOR phases)
-    gmg_j = api.GeometricMultigridSolver(st, api.WeightedJacobiSmoother(st, 0, L, 0.66), api.CGSolver(st, 0, 0, 50, 1e-16, 1e-16), 0, L, 3, 3)
+    gmg_j = api.GeometricMultigridSolver(st, api.WeightedJacobiSmoother(st, 0, L, 0.66), coarse_j or api.CGSolver(st, 0, 0, 50, 1e-16, 1e-16), max(LREP, 0), L, 3, 3)
     ms_vj = timed(lambda: gmg_j.solve(A, x, b, L), max(args.steps // 10, 2), 2)
 
     # end to end through the C-ABI with pinned HOST buffers: H2D src, apply, D2H dst every step.  n_lanes requests are kept in
@@ -459,7 +471,8 @@ def main():
                                              "note": "16 B x all DoFs / apply time (interior + interface kernels, overlapped on two streams)"}},
                 "also": {"jacobi_gdofs": gd(ms_jac), "jacobi_frac": BYTES_PER_DOF["jacobi"] * ndof_rank / (ms_jac * 1e-3) / 1e9 / peak,
                          "sor_gdofs": gd(ms_sor), "sor_frac": BYTES_PER_DOF["sor"] * ndof_rank / (ms_sor * 1e-3) / 1e9 / peak,
-                         "vcycle_3_3_gs_ms": ms_v, "vcycle_3_3_jacobi_ms": ms_vj, "ghost_exchanges_in_apply_region": ex0[0],
+                         "vcycle_3_3_gs_ms": ms_v, "vcycle_3_3_jacobi_ms": ms_vj, "vcycle_levels_replicated_on_every_rank": (list(range(0, LREP + 1)) if LREP >= 0 else []),
+                         "vcycle_level0_solver": ("dense Cholesky on the replica" if LREP >= 0 else "CG, 50 iterations max, tolerance 1e-16"), "ghost_exchanges_in_apply_region": ex0[0],
                          "e2e_solve": {"ms": ms_solve, "vcycles": solve_cycles, "residual_reduction": solve_red, "gdofs_solved_per_s": ndof / ms_solve / 1e6,
                                        "what": "upload b (pinned host), V(3,3) Gauss-Seidel cycles until |r| <= 1e-8 |r0| (one host-read dot per cycle), download x"},
                          "gs_factor_gap": "multicolour vs the reference's lexicographic hybrid, V(3,3) factor over cycles 6..10: -3.5 % cube_6el L5, "

@@ -294,6 +294,23 @@ def estimateRadius(A, level, max_iter, x, tmp):
     return out.value
 
 
+class DirectLevel0Solver(Solver):
+    """dense Cholesky of the level-0 operator on the free macro vertices (unpartitioned storage); the reference's PETScLUSolver role"""
+
+    def __init__(self, storage):
+        super().__init__(storage.lib, storage.lib.dll.hb_solver_create_direct_level0(storage.h), (storage,))
+
+
+class ReplicatedCoarseCycle(Solver):
+    """coarse-grid solver of a GeometricMultigridSolver on levels coarse_level .. L of a partitioned storage: the levels 0 .. coarse_level of
+    the cycle (V(pre, post), Gauss-Seidel or weighted Jacobi, CG on level 0 -- cg_max_iter = 0: direct solve) on a replica of the whole
+    mesh, redundantly on every rank"""
+
+    def __init__(self, storage, coarse_level, smoother="gs", omega=0.66, pre=3, post=3, cg_max_iter=50, cg_rel_tol=1e-16, cg_abs_tol=1e-16):
+        super().__init__(storage.lib, storage.lib.dll.hb_solver_create_replicated_coarse_cycle(
+            storage.h, coarse_level, 1 if smoother == "jacobi" else 0, omega, pre, post, cg_max_iter, cg_rel_tol, cg_abs_tol), (storage,))
+
+
 class GeometricMultigridSolver(Solver):
     def __init__(self, storage, smoother, coarse_solver, min_level, max_level, pre=3, post=3, increment=0, cycle=VCYCLE):
         super().__init__(storage.lib, storage.lib.dll.hb_solver_create_gmg(

@@ -74,6 +74,12 @@ _SIGNATURES = {
     "hb_p1function_add_scalar": (C.c_int, [_vp, C.c_double, C.c_int, C.c_int]),
     "hb_p1function_mult_elementwise": (C.c_int, [_vp, C.c_int, C.POINTER(_vp), C.c_int, C.c_int]),
     "hb_p1function_dot": (C.c_int, [_vp, _vp, C.c_int, C.c_int, _dp]),
+    "hb_storage_create_replica": (_vp, [_vp]),
+    "hb_p1function_get_boundary_condition": (C.c_int, [_vp, C.POINTER(C.c_int), C.c_int]),
+    "hb_solver_create_direct_level0": (_vp, [_vp]),
+    "hb_p1function_gather_to_replica": (C.c_int, [_vp, _vp, C.c_int]),
+    "hb_p1function_scatter_from_replica": (C.c_int, [_vp, _vp, C.c_int]),
+    "hb_solver_create_replicated_coarse_cycle": (_vp, [_vp, C.c_int, C.c_int, C.c_double, C.c_int, C.c_int, C.c_int, C.c_double, C.c_double]),
     "hb_p1function_dot_no_alloc": (C.c_int, [_vp, _vp, C.c_int, C.c_int, _vp]),  # out: DEVICE pointer
     "hb_p1function_sum": (C.c_int, [_vp, C.c_int, C.c_int, _dp]),
     "hb_p1function_max_magnitude": (C.c_int, [_vp, C.c_int, C.c_int, _dp]),

@@ -381,6 +381,7 @@ __global__ void __launch_bounds__( 256 ) hb_p2p_exchange_kernel( double* arena, 
 #endif
 
 int hb_p2p_grid_waves = 0; // tuning "p2p_grid_waves": CTAs of the stand-alone exchange kernel, in units of 148 (0: default)
+int hb_p2p_overlapped = 0; // set by the caller while the exchange is issued beside the interior kernel
 void hb_launch_p2p_exchange( double* arena, const HbP2PArgs& p, cudaStream_t st )
 {
 #ifndef HB_EMUL
@@ -396,7 +397,9 @@ void hb_launch_p2p_exchange( double* arena, const HbP2PArgs& p, cudaStream_t st 
       grid = 1;
    // every element is a chain of dependent accesses (offset -> value -> remote store; poll -> offset -> store): what moves the data
    // is the number of threads in flight, and no CTA waits for another one of its grid, so the grid may exceed one wave
-   const long long cap = 148ll * ( hb_p2p_grid_waves > 0 ? hb_p2p_grid_waves : 8 );
+   // (measured on 2 x B200, 10.7 MB per direction: alone 96 us on 148 CTAs, 72 us on 4 x 148 and more; beside the interior kernel of an
+   // apply the step takes 847 us with 148 CTAs and 890 us with 8 x 148 -- there the exchange should leave the SMs to the interior kernel)
+   const long long cap = 148ll * ( hb_p2p_grid_waves > 0 ? hb_p2p_grid_waves : ( hb_p2p_overlapped ? 1 : 8 ) );
    if ( grid > cap )
       grid = cap;
    hb_p2p_exchange_kernel<<< (unsigned) grid, 256, 0, st >>>( arena, p );

@@ -64,7 +64,7 @@ struct HbP2PArgs
    int32_t             gLo, gHi; // stand-alone exchange kernel: the groups gLo..gHi travel
 };
 void hb_launch_p2p_exchange( double* arena, const HbP2PArgs& p, cudaStream_t st );
-extern int hb_p2p_grid_waves;
+extern int hb_p2p_grid_waves, hb_p2p_overlapped;
 // whole SOR sweep of a small level in one single-CTA launch; false if the level is too large (or in the emulation build)
 // (px.np > 0: more than one rank, the sweep's ghost exchanges run inside the kernel over the peer-memory windows)
 bool hb_sor_small_fits( const HbLevelView& lv );

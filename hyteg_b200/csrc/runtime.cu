@@ -491,6 +491,99 @@ hb_storage* hb_storage_create_partitioned( int nV, const double* xyz, int nC, co
    HB_CATCH( nullptr )
 }
 
+/* The whole macro mesh of a partitioned storage on ONE rank: macro-cells in rank-major order (rank 0's cells in ascending id, then rank
+ * 1's, ...), same vertices, same mesh boundary flags.  Coarse multigrid levels are solved redundantly on such a replica -- a few thousand
+ * DoFs per level are cheaper to recompute on every rank than to keep consistent with six ghost exchanges per smoothing sweep. */
+hb_storage* hb_storage_create_replica( const hb_storage* src )
+{
+   HB_TRY
+   require( src != nullptr, "null storage" );
+   const hb::Topology& t = src->topo;
+   std::vector< int >  order;
+   for ( int r = 0; r < src->view.nRanks; r++ )
+      for ( int c = 0; c < t.nC; c++ )
+         if ( t.cellRank[(size_t) c] == r )
+            order.push_back( c );
+   require( (int) order.size() == t.nC, "cell ranks outside [0, n_ranks)" );
+   std::vector< int > cells;
+   for ( int c : order )
+      for ( int j = 0; j < 4; j++ )
+         cells.push_back( t.cellV[(size_t) c][(size_t) j] );
+   hb_storage* rep = hb_storage_create_partitioned( t.nV, t.xyz.data(), t.nC, cells.data(), 0, 1, nullptr );
+   if ( !rep )
+      return nullptr;
+   // mesh boundary flags: primitives are identified by their (sorted) vertex ids, which the replica shares with the original
+   hb::Topology&                          u = rep->topo;
+   std::map< std::array< int, 2 >, int > ef;
+   std::map< std::array< int, 3 >, int > ff;
+   for ( int e = 0; e < t.nE; e++ )
+      ef[t.edgeV[(size_t) e]] = t.eFlag[(size_t) e];
+   for ( int f = 0; f < t.nF; f++ )
+      ff[t.faceV[(size_t) f]] = t.fFlag[(size_t) f];
+   u.vFlag = t.vFlag;
+   for ( int e = 0; e < u.nE; e++ )
+      u.eFlag[(size_t) e] = ef.at( u.edgeV[(size_t) e] );
+   for ( int f = 0; f < u.nF; f++ )
+      u.fFlag[(size_t) f] = ff.at( u.faceV[(size_t) f] );
+   for ( int c = 0; c < u.nC; c++ )
+      u.cFlag[(size_t) c] = t.cFlag[(size_t) order[(size_t) c]];
+   rep->tablesDirty = true;
+   return rep;
+   HB_CATCH( nullptr )
+}
+
+static long long replicaOffsetCells( const hb_storage* part )
+{
+   long long n = 0;
+   for ( int c = 0; c < part->topo.nC; c++ )
+      if ( part->topo.cellRank[(size_t) c] < part->view.rank )
+         n++;
+   return n;
+}
+
+/* replica <- the owned macro-cell arrays of every rank (an all-gather, done as an all-reduce of zero-padded blocks so that the reducer a
+ * host installed for dotGlobal serves it as well); interface DoFs arrive consistent because every owned copy is */
+int hb_p1function_gather_to_replica( const hb_function* part, hb_function* rep, int level )
+{
+   HB_TRY
+   require( part && rep && rep->st->view.nRanks == 1 && rep->st->topo.nC == part->st->topo.nC, "gather_to_replica: not a replica of the function's storage" );
+   const size_t cs = (size_t) part->st->level( level ).view.cellSize, nLoc = (size_t) part->st->view.nLocal, nAll = (size_t) rep->st->view.nLocal;
+   const size_t off = (size_t) replicaOffsetCells( part->st );
+   require( off + nLoc <= nAll && nAll * cs < ( 1ull << 31 ), "gather_to_replica: level too large for a replica" );
+   cudaStream_t s = hb::currentStream();
+   cudaCheck( cudaMemsetAsync( rep->arena( level ), 0, nAll * cs * sizeof( double ), s ), "cudaMemsetAsync" );
+   cudaCheck( cudaMemcpyAsync( rep->arena( level ) + off * cs, part->arena( level ), nLoc * cs * sizeof( double ), cudaMemcpyDeviceToDevice, s ), "cudaMemcpyAsync D2D" );
+   if ( part->st->view.nRanks > 1 && !hb::deviceAllReduce( rep->arena( level ), (int) ( nAll * cs ), 0 ) )
+   {
+      require( hb::g_allreduce != nullptr, "gather_to_replica on a partitioned storage without a reducer: call hb_nccl_init or hb_set_allreduce first" );
+      cudaCheck( cudaStreamSynchronize( s ), "cudaStreamSynchronize" );
+#ifdef HB_EMUL
+      hb::g_allreduce( rep->arena( level ), (int) ( nAll * cs ), 0, hb::g_allreduceCtx );
+#else
+      std::vector< double > h( nAll * cs );
+      cudaCheck( cudaMemcpy( h.data(), rep->arena( level ), h.size() * sizeof( double ), cudaMemcpyDeviceToHost ), "cudaMemcpy D2H" );
+      hb::g_allreduce( h.data(), (int) h.size(), 0, hb::g_allreduceCtx );
+      cudaCheck( cudaMemcpy( rep->arena( level ), h.data(), h.size() * sizeof( double ), cudaMemcpyHostToDevice ), "cudaMemcpy H2D" );
+#endif
+   }
+   rep->touched( level );
+   return 0;
+   HB_CATCH( 1 )
+}
+
+/* owned macro-cell arrays <- their block of the replica (no communication) */
+int hb_p1function_scatter_from_replica( hb_function* part, const hb_function* rep, int level )
+{
+   HB_TRY
+   require( part && rep && rep->st->view.nRanks == 1 && rep->st->topo.nC == part->st->topo.nC, "scatter_from_replica: not a replica of the function's storage" );
+   const size_t cs = (size_t) part->st->level( level ).view.cellSize, nLoc = (size_t) part->st->view.nLocal, off = (size_t) replicaOffsetCells( part->st );
+   cudaCheck( cudaMemcpyAsync( part->arena( level ), rep->arena( level ) + off * cs, nLoc * cs * sizeof( double ), cudaMemcpyDeviceToDevice, hb::currentStream() ),
+              "cudaMemcpyAsync D2D" );
+   part->touched( level );
+   return 0;
+   HB_CATCH( 1 )
+}
+
 void hb_p2_storage_released( hb_storage* st ); // runtime_p2.inc
 void hb_storage_destroy( hb_storage* st )
 {

@@ -20,6 +20,7 @@ void         cudaCheck( cudaError_t e, const char* what );
 cudaStream_t currentStream();
 int          tuning( const std::string& key, int dflt );
 bool         p2pUsable(); // peer-memory windows connected and not switched off (tuning "p2p")
+bool         deviceAllReduce( double* dev, int n, int op ); // over the NCCL communicator, on the library's stream; false: no communicator
 // temporarily redirects the library's stream (ghost exchange on the side stream)
 struct StreamScope
 {

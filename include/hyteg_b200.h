@@ -91,6 +91,10 @@ hb_storage* hb_storage_create( int n_vertices, const double* xyz, int n_cells, c
 /* same with the target rank of every macro-cell given by the caller (SetupPrimitiveStorage::setTargetRank; what the load balancers of
  * src/hyteg/primitivestorage/loadbalancing/SimpleBalancer.hpp:56-78 compute).  cell_rank == NULL: contiguous blocks. */
 hb_storage* hb_storage_create_partitioned( int n_vertices, const double* xyz, int n_cells, const int* cells, int rank, int n_ranks, const int* cell_rank );
+/* the whole macro mesh of a partitioned storage on one rank (macro-cells in rank-major order, same vertices and mesh boundary flags): the
+ * storage of the replicated coarse levels, see hb_solver_create_replicated_coarse_cycle.  No counterpart in the reference, which keeps
+ * every level distributed (its coarse-grid agglomeration is left to PETSc, src/hyteg/petsc/PETScLUSolver.hpp). */
+hb_storage* hb_storage_create_replica( const hb_storage* st );
 void        hb_storage_destroy( hb_storage* st );
 /* SetupPrimitiveStorage::setMeshBoundaryFlagsOnBoundary (SetupPrimitiveStorage.cpp:977-988) */
 int hb_storage_set_mesh_boundary_flags_on_boundary( hb_storage* st, int flag_on_boundary, int flag_inner, int highest_dim_always_inner );
@@ -117,6 +121,7 @@ hb_function* hb_p1function_create( hb_storage* st, int min_level, int max_level 
 void         hb_p1function_destroy( hb_function* f );
 /* BoundaryCondition: meshBoundaryFlag -> DoFType; default create0123BC (0 Inner,1 Dirichlet,2 Neumann,3 Freeslip) */
 int hb_p1function_set_boundary_condition( hb_function* f, const int* dof_type_of_flag, int n );
+int hb_p1function_get_boundary_condition( const hb_function* f, int* dof_type_of_flag, int n );
 int hb_p1function_copy_boundary_condition( hb_function* dst, const hb_function* src ); /* copyBCs */
 hb_storage* hb_p1function_storage( const hb_function* f );
 int hb_p1function_level_range( const hb_function* f, int* min_level, int* max_level );
@@ -130,6 +135,10 @@ int hb_p1function_upload_async( hb_function* f, int level, const double* host );
 int hb_p1function_download_async( const hb_function* f, int level, double* host );
 int hb_p1function_upload_cell( hb_function* f, int level, int local_cell, const double* host );
 int hb_p1function_download_cell( const hb_function* f, int level, int local_cell, double* host );
+/* replica <- the owned macro-cell arrays of every rank (all-gather through the all-reduce of hb_nccl_init / hb_set_allreduce);
+ * owned macro-cell arrays <- their block of the replica (local copy) */
+int hb_p1function_gather_to_replica( const hb_function* f, hb_function* replica, int level );
+int hb_p1function_scatter_from_replica( hb_function* f, const hb_function* replica, int level );
 /* explicit ghost exchange (communicate); operators call it themselves when the mirrored layers are stale */
 int hb_p1function_communicate( hb_function* f, int level );
 /* raw device pointer of the local arena (for zero-copy interop, e.g. torch tensors) */
@@ -204,6 +213,18 @@ int hb_estimate_spectral_radius( hb_operator* op, hb_function* x, hb_function* t
 /* GeometricMultigridSolver (GeometricMultigridSolver.hpp:61-96) with P1 linear transfer operators */
 hb_solver* hb_solver_create_gmg( hb_storage* st, hb_solver* smoother, hb_solver* coarse_solver, int min_level, int max_level,
                                  int pre_smooth, int post_smooth, int smooth_increment, int cycle_type );
+/* Coarse-grid solver for a GeometricMultigridSolver on levels coarse_level .. L of a PARTITIONED storage: gathers x and b of level
+ * coarse_level onto a replica of the whole mesh and runs there, on every rank redundantly, the rest of the cycle -- V(pre,post) on levels
+ * 0 .. coarse_level with smoother 0 = Gauss-Seidel / 1 = weighted Jacobi( omega ) and CG( max_iter, rel_tol, abs_tol ) on level 0 -- i.e.
+ * the same operations GeometricMultigridSolver::solveRecursively (GeometricMultigridSolver.hpp:140-195) performs on those levels, without
+ * a single ghost exchange.  The macro-cell numbering of the replica differs from the partitioned one, so results agree with the fully
+ * distributed cycle up to rounding, not bitwise.  cg_max_iter == 0: level 0 is solved directly (hb_solver_create_direct_level0). */
+hb_solver* hb_solver_create_replicated_coarse_cycle( hb_storage* st, int coarse_level, int smoother, double omega, int pre, int post, int cg_max_iter,
+                                                     double cg_rel_tol, double cg_abs_tol );
+/* Direct solver for level 0 of an unpartitioned storage (the role PETScLUSolver plays as a coarse-grid solver in the reference,
+ * src/hyteg/petsc/PETScLUSolver.hpp): dense Cholesky of the free macro-vertex DoFs, assembled once per boundary-condition table by applying
+ * the operator to unit vectors; a solve is one download, two triangular sweeps on the host and one upload. */
+hb_solver* hb_solver_create_direct_level0( hb_storage* st );
 int        hb_solver_solve( hb_solver* s, hb_operator* op, hb_function* x, hb_function* b, int level ); /* Solver::solve */
 int        hb_solver_iterations( const hb_solver* s );
 void       hb_solver_destroy( hb_solver* s );

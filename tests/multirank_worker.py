@@ -107,6 +107,33 @@ def main():
             gmg.solve(t.A, fx, fb, L)
             t.A.residual(fx, fb, fr, L, Inner)
             res.append(np.sqrt(fr.dotGlobal(fr, L, Inner)))
+        if w > 1:
+            # the same cycles with the levels 0 .. L-1 on a replica of the whole mesh (no ghost exchange below level L): the same
+            # operations on another macro-cell numbering -> the same residual history up to rounding
+            c0, _ = comm.exchange_stats(lib)
+            fx.interpolate(lambda X, Y, Z: np.sin(X) * np.sinh(Y) + Z, L, DirichletBoundary)
+            fx.interpolate(0.0, L, Inner)
+            rep = api.ReplicatedCoarseCycle(t.st, L - 1, "gs", 0.66, 2, 2, 100, 1e-16, 1e-16)
+            gmr = api.GeometricMultigridSolver(t.st, api.GaussSeidelSmoother(t.st), rep, L - 1, L, 2, 2)
+            c1, _ = comm.exchange_stats(lib)
+            res_r = []
+            for _ in range(3):
+                gmr.solve(t.A, fx, fb, L)
+                t.A.residual(fx, fb, fr, L, Inner)
+                res_r.append(np.sqrt(fr.dotGlobal(fr, L, Inner)))
+            c2, _ = comm.exchange_stats(lib)
+            assert np.allclose(res_r, res, rtol=1e-9, atol=0), (res_r, res)
+            assert c2 - c1 < 40 * 3, (c1, c2)  # only level L exchanges: ~ 30 per cycle instead of ~ 30 per level
+            # ... and with level 0 solved directly (cg_max_iter = 0)
+            fx.interpolate(lambda X, Y, Z: np.sin(X) * np.sinh(Y) + Z, L, DirichletBoundary)
+            fx.interpolate(0.0, L, Inner)
+            gmd = api.GeometricMultigridSolver(t.st, api.GaussSeidelSmoother(t.st), api.ReplicatedCoarseCycle(t.st, L - 1, "gs", 0.66, 2, 2, 0), L - 1, L, 2, 2)
+            res_d = []
+            for _ in range(3):
+                gmd.solve(t.A, fx, fb, L)
+                t.A.residual(fx, fb, fr, L, Inner)
+                res_d.append(np.sqrt(fr.dotGlobal(fr, L, Inner)))
+            assert np.allclose(res_d, res, rtol=1e-7, atol=0), (res_d, res)
         return sor, t.get(fx, L), np.array(res)
 
     sor_p, x_p, res_p = run(rank, world)

@@ -81,3 +81,43 @@ def test_interface_coordinates_identical_in_all_copies(emul_lib):
     from oracle import p1_oracle as po
     o = po.P1Oracle(v, c, L, L)
     o.from_cells(f.download(L), L, check=True, tol=0.0)  # raises if two copies of a DoF differ
+
+
+@pytest.mark.parametrize("mesh", ["shell23", "cuboid322"])
+def test_direct_level0_solver_matches_cg(emul_lib, mesh):
+    """dense Cholesky of the level-0 operator on the free macro vertices == CG driven to round-off, also with non-zero Dirichlet data, and as
+    the coarse-grid solver of a V-cycle"""
+    from hyteg_b200 import api
+    import hyteg_b200 as hb
+    v, c = meshes.spherical_shell(2, 4, 0.5, 1.0) if mesh == "shell23" else meshes.cuboid(3, 2, 2)
+    st = api.PrimitiveStorage(v, c, lib=emul_lib)
+    st.setMeshBoundaryFlagsOnBoundary(1, 0, True)
+    L = 2
+    A = api.P1ConstantLaplaceOperator(st, 0, L)
+    x, y, b = (api.P1Function(n, st, 0, L) for n in "xyb")
+    g = lambda X, Y, Z: np.sin(2 * X) + Y * Z
+    for f in (x, y):
+        f.interpolate(0.0, 0, All)
+        f.interpolate(g, 0, DirichletBoundary)
+    b.interpolate(lambda X, Y, Z: 1.0 + X - Z, 0, All)
+    assert st.num_global_dofs(0) > 20
+    api.CGSolver(st, 0, 0, 500, 1e-30, 1e-13).solve(A, x, b, 0)
+    api.DirectLevel0Solver(st).solve(A, y, b, 0)
+    xa, ya = x.download(0), y.download(0)
+    assert np.abs(xa).max() > 0.1
+    assert np.abs(xa - ya).max() < 1e-10 * np.abs(xa).max(), np.abs(xa - ya).max()
+    # inside a V-cycle: same residual history as with CG on level 0
+    hist = []
+    for coarse in (api.CGSolver(st, 0, 0, 500, 1e-30, 1e-14), api.DirectLevel0Solver(st)):
+        gmg = api.GeometricMultigridSolver(st, api.GaussSeidelSmoother(st), coarse, 0, L, 2, 2)
+        x.interpolate(0.0, L, All)
+        x.interpolate(g, L, DirichletBoundary)
+        b.interpolate(0.0, L, All)
+        r = []
+        for _ in range(3):
+            gmg.solve(A, x, b, L)
+            A.residual(x, b, y, L, Inner)
+            r.append(np.sqrt(y.dotGlobal(y, L, Inner)))
+        hist.append(r)
+    assert np.allclose(hist[0], hist[1], rtol=1e-8, atol=0), hist
+    assert hist[0][-1] < 0.1 * hist[0][0]

@@ -10,13 +10,18 @@ lib = hb.get_lib(); lib.check(lib.dll.hb_device_init(local))
 if world > 1:  # torchrun: box of `world` cubes, one per rank (the bench's weak-scaling mesh)
     import torch.distributed as dist
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    comm.init_nccl(lib)
+    comm.init_nccl(lib, segment_bytes=256 << 20)
 for kv in filter(None, os.environ.get("HB_TUNING", "").split(",")):
     k, val = kv.split("="); lib.dll.hb_set_tuning(k.encode(), int(val))
 s = torch.cuda.current_stream(); lib.dll.hb_set_stream(s.cuda_stream)
-v, c = meshes.cube_6el() if world == 1 else meshes.cuboid(world, 1, 1, hi=(float(world), 1.0, 1.0))
 LMAX = 8
-st = api.PrimitiveStorage(v, c, rank, world); st.setMeshBoundaryFlagsOnBoundary(1, 0, True)
+if world == 1 and os.environ.get("MESH", "cube") == "cube":
+    v, c = meshes.cube_6el()
+    st = api.PrimitiveStorage(v, c, rank, world)
+else:  # the bench's weak-scaling mesh: one radial layer of the shell per rank
+    v, c = meshes.spherical_shell(2, world + 1, 0.5, 1.0)
+    st = api.PrimitiveStorage(v, c, rank, world, cell_rank=meshes.partition_radial_layers(v, c, world))
+st.setMeshBoundaryFlagsOnBoundary(1, 0, True)
 A = api.P1ConstantLaplaceOperator(st, 0, LMAX)
 x, b, r = (api.P1Function(n, st, 0, LMAX) for n in "xbr")
 R, P = api.P1toP1LinearRestriction(), api.P1toP1LinearProlongation()
@@ -39,8 +44,9 @@ for L in range(1, LMAX + 1):
     if rank == 0: print(f"L{L}: sor {sor:8.1f} us  residual {res:7.1f}  restrict {rs:7.1f}  prolongateAndAdd {pr:7.1f}  | V(3,3) share {lvl:8.1f} us")
 if rank == 0: print(f"sum over levels {tot/1e3:.2f} ms (plus CG on level 0)")
 # the coarse-grid solver and the whole cycle as the bench runs it
-cg = api.CGSolver(st, 0, 0, 100, 1e-16, 1e-16)
+cg = api.CGSolver(st, 0, 0, 50, 1e-16, 1e-16)  # as in bench.py
 b.interpolate(lambda X, Y, Z: X + Y * Z, 0, hb.All)
+if rank == 0: print("level 0:", st.num_global_dofs(0), "DoFs")
 def coarse():
     x.interpolate(0.0, 0, hb.Inner)
     cg.solve(A, x, b, 0)
