@@ -160,7 +160,8 @@ struct hb_operator
    bool    constUsable() const;
    bool    constAllLevels() const;
    int     constBase( int L ) const;
-   void    ensureConstWeights( int L );
+   int     constChunks() const;
+   void    ensureConstWeights( int L, int chunk = 0 );
    double* stage = nullptr; // pinned: [levels][nLocal][16] weights, then [levels][nLocal] flags
    ~hb_operator();
 };

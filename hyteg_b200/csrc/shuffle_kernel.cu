@@ -92,19 +92,20 @@ __global__ void __maxnreg__( 128 ) hb_shuffle_kernel( const HbLevelView lv, cons
    constexpr bool EX = ModeTraits< MODE >::hasExtra;
    const int      N  = lv.N;
    // item-major order: CTAs of consecutive block ids work on the same item of different macro-cells
-   int       itemIdx, cell;
-   const int nc = lv.nCells;
+   int       itemIdx, cl; // cl: macro-cell relative to the first one of this launch = entry of its weights behind constBase
+   const int nc = sa.cellCount;
    if ( sa.cellMajor )
    {
-      cell    = blockIdx.x / sa.nItems;
-      itemIdx = blockIdx.x - cell * sa.nItems;
+      cl      = blockIdx.x / sa.nItems;
+      itemIdx = blockIdx.x - cl * sa.nItems;
    }
    else
    {
       itemIdx = blockIdx.x / nc;
-      cell    = blockIdx.x - itemIdx * nc;
+      cl      = blockIdx.x - itemIdx * nc;
    }
-   if ( !( ( sa.selMask >> c_bflag[sa.constBase + cell] ) & 1 ) )
+   const int cell = sa.cellFirst + cl;
+   if ( !( ( sa.selMask >> c_bflag[sa.constBase + cl] ) & 1 ) )
       return;
    const HbItem it   = sa.items[itemIdx];
    const int    warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -117,7 +118,7 @@ __global__ void __maxnreg__( 128 ) hb_shuffle_kernel( const HbLevelView lv, cons
    const int    xc       = x0w - 1 + lane; // this lane's column
    const size_t cellBase = (size_t) cell * lv.cellSize;
 
-   const double* w    = c_W[sa.constBase + cell];
+   const double* w    = c_W[sa.constBase + cl];
    const double  invd = w[15]; // 1 / w[D_C], stored behind the 15 weights
 
    // ---- addressing ------------------------------------------------------------------------------------------------
@@ -384,7 +385,7 @@ void hb_shuffle_upload_weights( int first, int n, const double* w16, const uint8
 
 bool hb_shuffle_supported( int mode, const HbLevelView& lv )
 {
-   if ( lv.N < 32 || lv.nCells == 0 || lv.nCells > HB_CONST_W_ENTRIES )
+   if ( lv.N < 32 || lv.nCells == 0 )
       return false;
    return mode == HB_APPLY_REPLACE || mode == HB_APPLY_ADD || mode == HB_RESIDUAL || mode == HB_JACOBI || mode == HB_CHEB_FIRST ||
           mode == HB_CHEB_STEP || mode == HB_SOR;
@@ -423,7 +424,7 @@ static void launchDepth( int mode, unsigned g, unsigned b, const HbLevelView& lv
 
 void hb_launch_shuffle_stencil( int mode, const HbLevelView& lv, const HbStencilArgs& a, const HbStreamArgs& sa, cudaStream_t st, int depth )
 {
-   const long long grid = (long long) lv.nCells * sa.nItems;
+   const long long grid = (long long) sa.cellCount * sa.nItems;
    if ( grid < 1 )
       return;
    const unsigned g = (unsigned) grid, b = PAIRS * 32;

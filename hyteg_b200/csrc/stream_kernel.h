@@ -25,4 +25,6 @@ struct HbStreamArgs
    uint32_t      selMask;   // bit f set: macro primitives with meshBoundaryFlag f are selected by (bc, flag)
    int32_t       constBase; // first entry of this level's weights in constant memory
    int32_t       cellMajor; // block id = cell * nItems + item (else item * nCells + cell)
+   int32_t       cellFirst, cellCount; // the launch covers the macro-cells [cellFirst, cellFirst + cellCount), whose weights sit in the
+                                       // constant-memory entries constBase .. (more local macro-cells than entries: several launches)
 };

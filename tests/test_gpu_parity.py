@@ -279,3 +279,39 @@ def test_sor_cooperative_interface_matches_multi_launch(cuda_lib, name, L):
         cuda_lib.dll.hb_set_tuning(b"sor_coop", -2147483648)
     assert np.array_equal(a, g), np.abs(a - g).max()
     assert np.array_equal(h, g), np.abs(h - g).max()
+
+
+def test_interior_kernel_in_chunks_beyond_the_constant_weight_table(cuda_lib):
+    """more local macro-cells (480) than constant-memory weight entries (448): the interior kernel runs chunk by chunk with the chunk's
+    weights uploaded in front of every launch -- apply, Jacobi and SOR against the generic kernel"""
+    v, c = meshes.cuboid(5, 4, 4)
+    assert len(c) == 480
+    L = 5
+    st = api.PrimitiveStorage(v, c, lib=cuda_lib)
+    st.setMeshBoundaryFlagsOnBoundary(1, 0, True)
+    A = api.P1ConstantLaplaceOperator(st, L, L)
+    f = {k: api.P1Function(k, st, L, L) for k in ("src", "rhs", "dst")}
+
+    def run(shuffle):
+        cuda_lib.dll.hb_set_tuning(b"interior", 2 if shuffle else 0)
+        cuda_lib.dll.hb_set_tuning(b"sor_shuffle", shuffle)
+        f["src"].interpolate(lambda X, Y, Z: np.sin(5 * X) * np.cos(3 * Y) + Z * X, L, All)
+        f["rhs"].interpolate(lambda X, Y, Z: np.cos(X + 2 * Y) * Z, L, All)
+        out = {}
+        A.apply(f["src"], f["dst"], L, All)
+        out["apply"] = f["dst"].download(L)
+        A.smooth_jac(f["dst"], f["rhs"], f["src"], 0.66, L, pc.SMOOTH)
+        out["jacobi"] = f["dst"].download(L)
+        A.smooth_sor(f["src"], f["rhs"], 1.1, L, pc.SMOOTH)
+        A.smooth_sor(f["src"], f["rhs"], 1.1, L, pc.SMOOTH, backwards=True)
+        out["sor"] = f["src"].download(L)
+        return out
+
+    try:
+        a, g = run(1), run(0)
+    finally:
+        cuda_lib.dll.hb_set_tuning(b"interior", -2147483648)
+        cuda_lib.dll.hb_set_tuning(b"sor_shuffle", -2147483648)
+    for k in a:
+        assert np.abs(a[k] - g[k]).max() <= 1e-12 * np.abs(g[k]).max(), (k, np.abs(a[k] - g[k]).max())
+    assert np.abs(a["apply"]).max() > 1e-5
