@@ -28,5 +28,15 @@ for L in (0, 2, 4):
          "add": wall(lambda: z.add([0.5], [x], L, hb.Inner)),
          "interpolate const": wall(lambda: z.interpolate(0.0, L, hb.All)),
          "sor": wall(lambda: A.smooth_sor(x, y, 1.0, L, hb.SMOOTH_FLAG))}
+    def cg_like():  # one CG iteration's worth of operations, in CG's order
+        A.apply(x, y, L, hb.Inner); x.dotGlobal(y, L, hb.Inner); z.add([0.5], [x], L, hb.Inner); z.add([-0.5], [y], L, hb.Inner)
+        z.dotGlobal(z, L, hb.Inner); y.interpolate(0.0, L, hb.All); y.assign([1.0], [z], L, hb.Inner); z.dotGlobal(y, L, hb.Inner)
+        x.assign([1.0, 0.3], [y, x], L, hb.Inner)
+    r["one CG iteration's operations"] = wall(cg_like, 20)
+    cg = api.CGSolver(st, L, L, 10, 1e-30, 1e-300)
+    y.interpolate(lambda X, Y, Z: X + Y * Z, L, hb.All)
+    def solve():
+        z.interpolate(0.0, L, hb.Inner); cg.solve(A, z, y, L)
+    r["CGSolver, 10 iterations"] = wall(solve, 5)
     if rank == 0: print(f"L{L} on {world} ranks (us wall):", ", ".join(f"{k} {v:.1f}" for k, v in r.items()), flush=True)
 lib.dll.hb_nccl_finalize(); dist.destroy_process_group()
