@@ -74,6 +74,19 @@ def main():
             gmg.solve(A, fx, fb, L)
             A.residual(fx, fb, fr, L, Inner)
             res.append(np.sqrt(fr.dotGlobal(fr, L, Inner)))
+        if w > 1:
+            # the same cycles with levels 0 .. 3 on a replica of the whole mesh (gathered through the NCCL all-reduce) and level 0
+            # solved directly: the same iteration up to rounding
+            xs = fx.download(L).copy()
+            fx.interpolate(0.0, L, Inner)
+            rep = api.GeometricMultigridSolver(t, api.GaussSeidelSmoother(t), api.ReplicatedCoarseCycle(t, 3, "gs", 0.66, 3, 3, 0), 3, L, 3, 3)
+            res_r = []
+            for _ in range(3):
+                rep.solve(A, fx, fb, L)
+                A.residual(fx, fb, fr, L, Inner)
+                res_r.append(np.sqrt(fr.dotGlobal(fr, L, Inner)))
+            assert np.allclose(res_r, res, rtol=1e-7, atol=0), (res_r, res)
+            assert np.abs(fx.download(L) - xs).max() <= 1e-9 * np.abs(xs).max()
         return t.local_cell_global_ids(), ap, so, fx.download(L).copy(), np.array(res)
 
     cells_p, ap_p, so_p, x_p, res_p = run(rank, world)
