@@ -32,6 +32,8 @@
 #include "hyteg/primitivestorage/PrimitiveStorage.hpp"
 #include "hyteg/solvers/Smoothables.hpp"
 
+#include "constant_stencil_operator/P1ConstantOperator.hpp" // 2D storages stay on the reference's own operator
+
 #include "hyteg_b200.h"
 
 namespace hyteg {
@@ -241,13 +243,24 @@ class P1ConstantLaplaceOperatorB200 : public Operator< P1Function< real_t >, P1F
  public:
    P1ConstantLaplaceOperatorB200( const std::shared_ptr< PrimitiveStorage >& storage, size_t minLevel, size_t maxLevel )
    : Operator( storage, minLevel, maxLevel )
-   , dev_( B200StorageMirror::of( storage ) )
    {
-      op_ = hb_p1_constant_laplace_create( dev_->handle(), int( minLevel ), int( maxLevel ) );
+      if ( !storage->hasGlobalCells() )
+      {
+         // the library covers the 3D (macro-cell) path; a 2D macro mesh keeps the reference's operator, so that drivers which loop over
+         // 2D and 3D meshes run unchanged
+         ref2D_ = std::make_shared< P1ConstantLaplaceOperator >( storage, minLevel, maxLevel );
+         return;
+      }
+      dev_ = B200StorageMirror::of( storage );
+      op_  = hb_p1_constant_laplace_create( dev_->handle(), int( minLevel ), int( maxLevel ) );
       if ( !op_ )
          WALBERLA_ABORT( "hyteg_b200: " << hb_last_error() );
    }
-   ~P1ConstantLaplaceOperatorB200() override { hb_operator_destroy( op_ ); }
+   ~P1ConstantLaplaceOperatorB200() override
+   {
+      if ( op_ )
+         hb_operator_destroy( op_ );
+   }
    P1ConstantLaplaceOperatorB200( const P1ConstantLaplaceOperatorB200& )            = delete;
    P1ConstantLaplaceOperatorB200& operator=( const P1ConstantLaplaceOperatorB200& ) = delete;
 
@@ -258,6 +271,8 @@ class P1ConstantLaplaceOperatorB200 : public Operator< P1Function< real_t >, P1F
                DoFType                     flag,
                UpdateType                  updateType = Replace ) const override
    {
+      if ( ref2D_ )
+         return ref2D_->apply( src, dst, level, flag, updateType );
       hb_function* s = dev_->upload( src, level );
       hb_function* d = dev_->upload( dst, level ); // Add needs dst; Replace keeps the DoFs outside `flag`
       HB_BRIDGE_CHECK( hb_operator_apply( op_, s, d, int( level ), int( flag ), updateType == Replace ? 0 : 1 ) );
@@ -289,6 +304,8 @@ class P1ConstantLaplaceOperatorB200 : public Operator< P1Function< real_t >, P1F
                     size_t                      level,
                     DoFType                     flag ) const override
    {
+      if ( ref2D_ )
+         return ref2D_->smooth_jac( dst, rhs, src, relax, level, flag );
       hb_function* d = dev_->upload( dst, level );
       hb_function* r = dev_->upload( rhs, level );
       hb_function* s = dev_->upload( src, level );
@@ -304,6 +321,12 @@ class P1ConstantLaplaceOperatorB200 : public Operator< P1Function< real_t >, P1F
    /// P1Operator::computeInverseDiagonalOperatorValues (p1functionspace/P1Operator.hpp:178-200): all levels, from the device stencils
    void computeInverseDiagonalOperatorValues() override
    {
+      if ( ref2D_ )
+      {
+         ref2D_->computeInverseDiagonalOperatorValues();
+         inverseDiagonal_ = ref2D_->getInverseDiagonalValues();
+         return;
+      }
       if ( !inverseDiagonal_ )
          inverseDiagonal_ = std::make_shared< P1Function< real_t > >( "inverse diagonal (b200)", storage_, minLevel_, maxLevel_ );
       for ( uint_t level = minLevel_; level <= maxLevel_; level++ )
@@ -323,14 +346,23 @@ class P1ConstantLaplaceOperatorB200 : public Operator< P1Function< real_t >, P1F
  private:
    void sor( const P1Function< real_t >& dst, const P1Function< real_t >& rhs, real_t relax, size_t level, DoFType flag, int backwards ) const
    {
+      if ( ref2D_ )
+      {
+         if ( backwards )
+            ref2D_->smooth_sor_backwards( dst, rhs, relax, level, flag );
+         else
+            ref2D_->smooth_sor( dst, rhs, relax, level, flag );
+         return;
+      }
       hb_function* d = dev_->upload( dst, level );
       hb_function* r = dev_->upload( rhs, level );
       HB_BRIDGE_CHECK( hb_operator_smooth_sor( op_, d, r, double( relax ), int( level ), int( flag ), backwards ) );
       dev_->download( dst, level );
    }
 
-   std::shared_ptr< B200StorageMirror >    dev_;
-   hb_operator*                            op_ = nullptr;
+   std::shared_ptr< B200StorageMirror >         dev_;
+   hb_operator*                                 op_ = nullptr;
+   std::shared_ptr< P1ConstantLaplaceOperator > ref2D_; // set instead of dev_ / op_ on 2D storages
    std::shared_ptr< P1Function< real_t > > inverseDiagonal_;
 };
 

@@ -39,7 +39,8 @@ ROOT = os.path.dirname(HERE)
 BRIDGE = os.path.join(ROOT, "integration", "hyteg_bridge")
 # unmodified reference tests compiled twice: as they are (the CPU reference) and with P1ConstantLaplaceOperator swapped for the bridge
 BRIDGE_TESTS = ["tests/hyteg/convergence/P1GMG3DConvergenceTest.cpp", "tests/hyteg/convergence/P1CG3DConvergenceTest.cpp",
-                "tests/hyteg/P1/P1LaplaceOperator3DTest.cpp"]
+                "tests/hyteg/P1/P1LaplaceOperator3DTest.cpp", "tests/hyteg/convergence/P1GSConvergenceTest.cpp",
+                "tests/hyteg/convergence/P1JacobiConvergenceTest.cpp"]
 
 # sub-trees of the reference that make up the path (walberla::core, libhyteg, the P1 part of
 # constant_stencil_operator).  Directories that need packages this image does not have are left out.
@@ -151,10 +152,11 @@ def fresh(out, deps):
 
 def build_bridge_tests(lib):
     import shutil
-    os.makedirs(os.path.join(OUT, "meshes", "3D"), exist_ok=True)
-    for f in os.listdir(REF + "/data/meshes/3D"):
-        if f.endswith(".msh") and os.path.getsize(REF + "/data/meshes/3D/" + f) < (1 << 20):
-            shutil.copyfile(REF + "/data/meshes/3D/" + f, os.path.join(OUT, "meshes", "3D", f))
+    for sub in ("3D", "2D"):
+        os.makedirs(os.path.join(OUT, "meshes", sub), exist_ok=True)
+        for f in os.listdir(REF + "/data/meshes/" + sub):
+            if f.endswith(".msh") and os.path.getsize(REF + "/data/meshes/" + sub + "/" + f) < (1 << 20):
+                shutil.copyfile(REF + "/data/meshes/" + sub + "/" + f, os.path.join(OUT, "meshes", sub, f))
     link = ["-Wl,--start-group", lib, "-Wl,--end-group", "-lpthread"]
     for t in BRIDGE_TESTS:
         src, name = os.path.join(REF, t), os.path.basename(t)[:-4]

@@ -3,6 +3,8 @@ integration/hyteg_bridge/ (oracle/build_ref.py compiles /root/reference/tests/hy
 is edited or copied).  A binary exits 0 only if every WALBERLA_CHECK of the reference test held, e.g. the per-cycle residual reduction
 < 3.2e-2 of tests/hyteg/convergence/P1GMG3DConvergenceTest.cpp:151.
 
+Also built this way: convergence/P1GSConvergenceTest.cpp and convergence/P1JacobiConvergenceTest.cpp, which loop over 2D and 3D meshes.
+
   <Test>_ref    the test as the reference builds it (its CPU operator)                      -- the expected log
   <Test>_emul   bridge + tests/emul/libhyteg_b200_emul.so (kernels run on the host)          -- CPU suite
   <Test>_b200   bridge + hyteg_b200/libhyteg_b200.so (the CUDA kernels)                      -- `-m gpu`
@@ -15,7 +17,7 @@ import pytest
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 REF = os.path.join(ROOT, "oracle", "_ref")
-TESTS = ["P1GMG3DConvergenceTest", "P1CG3DConvergenceTest", "P1LaplaceOperator3DTest"]
+TESTS = ["P1GMG3DConvergenceTest", "P1CG3DConvergenceTest", "P1LaplaceOperator3DTest", "P1GSConvergenceTest", "P1JacobiConvergenceTest"]
 NUM = r"[-+]?\d\.?\d*(?:e[-+]?\d+)?"
 
 
@@ -55,6 +57,17 @@ def compare(name, log, ref):
         for (la, ra, ea), (lb, rb, eb) in zip(a, b):
             assert la == lb and float(ra) < 1e-16
             assert abs(float(ea) - float(eb)) < 1e-6 * float(eb)  # CG solves the same system to round-off: same discretisation error
+    elif name in ("P1GSConvergenceTest", "P1JacobiConvergenceTest"):
+        # 20 sweeps on 2D meshes (the bridge keeps the reference's operator there) and on 3D/tet_1el, 3D/regular_octahedron_8el (device);
+        # the test itself checks that the residual falls in every sweep
+        a = [float(x) for x in re.findall(r"discrete L2 error = (%s)" % NUM, log)]
+        b = [float(x) for x in re.findall(r"discrete L2 error = (%s)" % NUM, ref)]
+        assert len(a) == len(b) >= 3
+        for ea, eb in zip(a, b):
+            if name == "P1JacobiConvergenceTest":
+                assert abs(ea - eb) <= 1e-5 * eb  # the same iteration
+            else:
+                assert abs(ea - eb) <= 0.25 * eb  # multicolour against lexicographic ordering after 20 sweeps (2D cases: identical)
     else:
         a = [float(x) for x in re.findall(r"L2 error: (%s)" % NUM, log)]
         b = [float(x) for x in re.findall(r"L2 error: (%s)" % NUM, ref)]
