@@ -40,7 +40,7 @@ BRIDGE = os.path.join(ROOT, "integration", "hyteg_bridge")
 # unmodified reference tests compiled twice: as they are (the CPU reference) and with P1ConstantLaplaceOperator swapped for the bridge
 BRIDGE_TESTS = ["tests/hyteg/convergence/P1GMG3DConvergenceTest.cpp", "tests/hyteg/convergence/P1CG3DConvergenceTest.cpp",
                 "tests/hyteg/P1/P1LaplaceOperator3DTest.cpp", "tests/hyteg/convergence/P1GSConvergenceTest.cpp",
-                "tests/hyteg/convergence/P1JacobiConvergenceTest.cpp"]
+                "tests/hyteg/convergence/P1JacobiConvergenceTest.cpp", "tests/hyteg/operators/P1ElementwiseOperatorTest.cpp"]
 
 # sub-trees of the reference that make up the path (walberla::core, libhyteg, the P1 part of
 # constant_stencil_operator).  Directories that need packages this image does not have are left out.

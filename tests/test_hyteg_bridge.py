@@ -17,7 +17,7 @@ import pytest
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 REF = os.path.join(ROOT, "oracle", "_ref")
-TESTS = ["P1GMG3DConvergenceTest", "P1CG3DConvergenceTest", "P1LaplaceOperator3DTest", "P1GSConvergenceTest", "P1JacobiConvergenceTest"]
+TESTS = ["P1GMG3DConvergenceTest", "P1CG3DConvergenceTest", "P1LaplaceOperator3DTest", "P1GSConvergenceTest", "P1JacobiConvergenceTest", "P1ElementwiseOperatorTest"]
 NUM = r"[-+]?\d\.?\d*(?:e[-+]?\d+)?"
 
 
@@ -57,6 +57,10 @@ def compare(name, log, ref):
         for (la, ra, ea), (lb, rb, eb) in zip(a, b):
             assert la == lb and float(ra) < 1e-16
             assert abs(float(ea) - float(eb)) < 1e-6 * float(eb)  # CG solves the same system to round-off: same discretisation error
+    elif name == "P1ElementwiseOperatorTest":
+        # the reference's on-the-fly elementwise operator A against the constant-stencil operator B (here: the device) on a 2D and a 3D mesh
+        a = [float(x) for x in re.findall(r"\|\|\(A - B\)u\|\|_inf = (%s)" % NUM, log)]
+        assert len(a) >= 2 and max(a) < 1e-14, a
     elif name in ("P1GSConvergenceTest", "P1JacobiConvergenceTest"):
         # 20 sweeps on 2D meshes (the bridge keeps the reference's operator there) and on 3D/tet_1el, 3D/regular_octahedron_8el (device);
         # the test itself checks that the residual falls in every sweep
