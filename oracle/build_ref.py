@@ -157,7 +157,7 @@ def build_bridge_tests(lib):
         for f in os.listdir(REF + "/data/meshes/" + sub):
             if f.endswith(".msh") and os.path.getsize(REF + "/data/meshes/" + sub + "/" + f) < (1 << 20):
                 shutil.copyfile(REF + "/data/meshes/" + sub + "/" + f, os.path.join(OUT, "meshes", sub, f))
-    link = ["-Wl,--start-group", lib, "-Wl,--end-group", "-lpthread"]
+    link = ["-s", "-Wl,--start-group", lib, "-Wl,--end-group", "-lpthread"]  # stripped: the binaries travel to the GPU box with every gpurun call
     for t in BRIDGE_TESTS:
         src, name = os.path.join(REF, t), os.path.basename(t)[:-4]
         inc = ["-I" + REF + "/src/constant_stencil_operator/..", "-I" + REF + "/tests"]
