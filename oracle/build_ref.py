@@ -8,7 +8,7 @@ generated kernels ON, no MPI / PETSc / ADIOS2 / Trilinos / MPFR).
 
 Outputs (all under oracle/_ref/, git-ignored, shipped to the GPU box with the snapshot):
   obj/*.o                 one object per reference translation unit
-  libhyteg_ref.a          walberla::core + libhyteg + constant_stencil_operator (P1 part)
+  cpu_only/libhyteg_ref.a walberla::core + libhyteg + constant_stencil_operator (P1 part)
   ref_dump                oracle/ref_dump.cpp linked against it: dumps golden fixtures (tests/golden/ref_*.npz
                           are written by oracle/make_ref_fixtures.py from its output) and is the
                           `bench.py --impl reference` CPU arm
@@ -17,7 +17,7 @@ Outputs (all under oracle/_ref/, git-ignored, shipped to the GPU box with the sn
   <Test>_ref              an UNMODIFIED reference test (BRIDGE_TESTS), built as it is
   <Test>_b200             the same source with -include integration/hyteg_bridge/swap_P1ConstantLaplaceOperator.hpp: every use of
                           P1ConstantLaplaceOperator becomes the bridge class, linked against hyteg_b200/libhyteg_b200.so
-  <Test>_emul             ditto against tests/emul/libhyteg_b200_emul.so (the kernels run sequentially on the host; CPU suite)
+  cpu_only/<Test>_emul    ditto against tests/emul/libhyteg_b200_emul.so (the kernels run sequentially on the host; CPU suite)
 
 Usage: python oracle/build_ref.py [-j N] [--only-driver]
 """
@@ -27,6 +27,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 REF = os.environ.get("HYTEG_REF", "/root/reference")
 OUT = os.path.join(HERE, "_ref")
 OBJ = os.path.join(OUT, "obj")
+CPU = os.path.join(OUT, "cpu_only")  # what the GPU box does not need (listed in .gpurunignore): the archive, the emulation binaries
 CXX = os.environ.get("CXX", "g++")
 # x86-64-v3 (AVX2+FMA) instead of -march=native: the library travels to another host (the GPU box).
 FLAGS = ["-O3", "-march=x86-64-v3", "-std=c++20", "-fPIC", "-w", "-DNDEBUG", "-fopenmp-simd",
@@ -99,7 +100,8 @@ def main():
         print("reference tree not present (%s): keeping prebuilt oracle/_ref" % REF)
         return 0
     os.makedirs(OBJ, exist_ok=True)
-    lib = os.path.join(OUT, "libhyteg_ref.a")
+    os.makedirs(CPU, exist_ok=True)
+    lib = os.path.join(CPU, "libhyteg_ref.a")
     if not a.only_driver or not os.path.exists(lib):
         srcs = sources()
         failed = []
@@ -172,11 +174,12 @@ def build_bridge_tests(lib):
             if not os.path.exists(os.path.join(d, "lib" + l + ".so")):
                 print("skipping", name + tag, "(lib%s.so not built yet)" % l)
                 continue
-            rel = os.path.relpath(d, OUT)
-            if fresh(os.path.join(OUT, name + tag), [o, lib, os.path.join(d, "lib" + l + ".so")]):
+            exe = os.path.join(CPU if tag == "_emul" else OUT, name + tag)
+            rel = os.path.relpath(d, os.path.dirname(exe))
+            if fresh(exe, [o, lib, os.path.join(d, "lib" + l + ".so")]):
                 continue
-            subprocess.check_call([CXX, o, "-o", os.path.join(OUT, name + tag)] + link + ["-L" + d, "-l" + l, "-Wl,-rpath,$ORIGIN/" + rel])
-            print("built", os.path.join(OUT, name + tag))
+            subprocess.check_call([CXX, o, "-o", exe] + link + ["-L" + d, "-l" + l, "-Wl,-rpath,$ORIGIN/" + rel])
+            print("built", exe)
 
 
 if __name__ == "__main__":

@@ -22,7 +22,7 @@ NUM = r"[-+]?\d\.?\d*(?:e[-+]?\d+)?"
 
 
 def run(name, tag, tmp_path):
-    exe = os.path.join(REF, name + "_" + tag)
+    exe = os.path.join(REF, "cpu_only" if tag == "emul" else "", name + "_" + tag)
     if not os.path.exists(exe):
         pytest.skip("%s not built (oracle/build_ref.py needs the reference tree)" % os.path.basename(exe))
     # the tests write their partitioning VTK files to ../../output
